@@ -1,0 +1,175 @@
+/*
+ * gradavg.h -- C ABI of the B200 gradient-averaging library (libgradavg.so).
+ *
+ * One hot path, rebuilt from scratch for sm_100a: the post-backward gradient averaging of
+ * dblakely/pytorch-distributed-example,
+ *
+ *     for p in self.net.parameters():                                  mnist/main.py:125
+ *         distributed.all_reduce(p.grad.data, op=reduce_op.SUM)        mnist/main.py:126
+ *         p.grad.data /= float(world_size)                             mnist/main.py:127
+ *
+ * and its toy analogue (one int32 all_reduce SUM, toy/main.py:19-20).  Everything below is
+ * plain C: pointers, sizes, ints.  No torch types cross this boundary; a stream is passed as
+ * the `cudaStream_t` value cast to `void*` (NULL = the legacy default stream).
+ *
+ * Conventions
+ *   - every function returns 0 on success and a negative GA_E* code on failure; the message
+ *     for the calling thread's last failure is `ga_last_error()`.  Nothing throws.
+ *   - a context hosts `n_local` consecutive ranks of a `world`-rank job on ONE device.  The
+ *     normal case is one process per GPU: n_local = 1 (`ga_create`).  `ga_create_local` hosts
+ *     all `world` ranks on one device in one process (single launch, blockIdx.y = rank); it is
+ *     the same kernels and flag protocol and is how the parity tests run on a one-GPU box.
+ *   - calls are collective: every rank calls the same function with the same sizes, in the
+ *     same order.  Calls on one context must come from one thread at a time.
+ *   - sums are taken in rank order, ((g0 + g1) + g2) + ..., each add one IEEE binary32
+ *     operation, then ONE IEEE division by (float)world.  Results are therefore identical on
+ *     every rank and bit-identical to oracle/fold.c.
+ */
+#ifndef GRADAVG_H_
+#define GRADAVG_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GA_MAX_WORLD        8      /* ranks behind one NVSwitch domain */
+#define GA_IPC_HANDLE_BYTES 64     /* sizeof(cudaIpcMemHandle_t) */
+
+/* error codes */
+#define GA_OK            0
+#define GA_EINVAL       -1   /* bad argument (message says which) */
+#define GA_ECUDA        -2   /* a CUDA runtime call failed (message carries cudaGetErrorString) */
+#define GA_ECAPACITY    -3   /* gradient set / byte count does not fit the bucket capacity */
+#define GA_ESTATE       -4   /* wrong call order (peers not opened, context broken, ...) */
+#define GA_ETIMEOUT     -5   /* a kernel gave up waiting for a peer's flag (see ga_status) */
+
+/* variant of the reduction */
+#define GA_VARIANT_AUTO     0   /* chosen from the byte count, see ga_set_option(GA_OPT_ONESHOT_MAX_BYTES) */
+#define GA_VARIANT_ONESHOT  1   /* every rank reads all `world` buckets: 1 barrier, (world-1)*S ingress */
+#define GA_VARIANT_TWOSHOT  2   /* reduce-scatter + all-gather by peer reads: 2 barriers, 2(world-1)/world*S */
+
+/* element type + operation */
+#define GA_OP_F32_AVG   0   /* fp32: rank-order sum, then / (float)world      mnist/main.py:126-127 */
+#define GA_OP_I32_SUM   1   /* int32: sum, no division                          toy/main.py:19-20   */
+#define GA_OP_F32_SUM   2   /* fp32: rank-order sum only (all_reduce alone)    mnist/main.py:126   */
+
+/* options for ga_set_option */
+#define GA_OPT_ONESHOT_MAX_BYTES 1   /* AUTO uses one-shot when bytes <= value */
+#define GA_OPT_TIMEOUT_MS        2   /* flag-wait timeout inside kernels; 0 = wait forever */
+#define GA_OPT_MAX_BLOCKS        3   /* cap on thread blocks per rank (0 = fill the device) */
+
+typedef struct ga_ctx ga_ctx;
+
+/* Last error message of the calling thread ("" if none). */
+const char *ga_last_error(void);
+
+/*
+ * Create the per-process context of rank `rank` in a `world`-rank job on CUDA device `device`.
+ * Replaces the state `distributed.init_process_group` sets up for this path
+ * (mnist/main.py:198-204, toy/main.py:28-33) plus `distributed.get_world_size()`
+ * (mnist/main.py:123), which becomes a field of the context.
+ * cudaMallocs, owned by the context and freed by ga_destroy:
+ *   - the persistent flat bucket of `capacity_bytes` (rounded up to 2 KiB tiles) preceded by
+ *     the flag pad (one IPC-exportable allocation),
+ *   - a same-size local result region used by the bucket-direct calls.
+ */
+int ga_create(int rank, int world, int device, size_t capacity_bytes, ga_ctx **out);
+
+/*
+ * Same, but all `world` ranks live in this process on this one device; no IPC, peers are
+ * opened implicitly.  Tensor-list arguments then carry world * n_tensors pointers,
+ * rank-major.  No counterpart call in the reference: its READMEs start the ranks as separate
+ * processes on one host (mnist/README.md:18-33); this is that, for one GPU.
+ */
+int ga_create_local(int world, int device, size_t capacity_bytes, ga_ctx **out);
+
+/* CUDA-IPC handle of this rank's bucket allocation; exchange the 64 bytes once over the
+ * process group the script already created (mnist/main.py:199-203). */
+int ga_export_handle(ga_ctx *ctx, unsigned char out[GA_IPC_HANDLE_BYTES]);
+
+/* `handles` = world * 64 bytes, rank order (own entry ignored).  Opens every peer's bucket
+ * (cudaIpcOpenMemHandle, peer access enabled lazily).  Call once, after every rank exported. */
+int ga_open_peers(ga_ctx *ctx, const unsigned char *handles);
+
+/*
+ * The hot path: Trainer.average_gradients (mnist/main.py:122-127) for one parameter list.
+ * grad_ptrs[i] / numel[i]: device pointer and element count of the i-th contiguous fp32
+ * gradient, in parameters() order (n_local * n_tensors pointers for a local world).  Pointers
+ * are re-read every call because autograd re-allocates `.grad` each step.
+ * Enqueues ONE kernel on `stream`: pack into the bucket -> peer reduce in rank order (+ the
+ * division) -> unpack straight into the same gradient tensors.  Asynchronous; the gradients
+ * are borrowed until the enqueued work completes.
+ */
+int ga_average(ga_ctx *ctx, const void *const *grad_ptrs, const int64_t *numel, int n_tensors,
+               void *stream, int variant);
+
+/* Generalisation of ga_average over the element op (GA_OP_I32_SUM covers toy/main.py:19-20,
+ * where the tensor list is one 1-element int32 tensor). */
+int ga_allreduce_tensors(ga_ctx *ctx, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                         int op, void *stream, int variant);
+
+/*
+ * Bucket-direct form, for the size sweep and the same-buffer comparison with NCCL: the caller
+ * has written `nbytes` into ga_send_ptr() (stream-ordered before this call); the averaged
+ * result is left in ga_recv_ptr().  Returns (stream-wise) only after every peer has finished
+ * reading this rank's bucket, so the caller may refill it at once.
+ */
+int ga_allreduce_bucket(ga_ctx *ctx, size_t nbytes, int op, void *stream, int variant);
+
+/*
+ * Host-buffer form of ga_average, the call a CPU-side user of the reference makes (its
+ * default gloo path keeps gradients in host memory, mnist/main.py:181-182 with --no-cuda):
+ * copies each host tensor into its bucket slot (H2D), runs the bucket-direct reduction,
+ * copies the results back over the same host tensors (D2H), all on `stream`.  Host memory
+ * should be pinned for the copies to be asynchronous.  n_local must be 1 unless the context is
+ * a local world, in which case host_ptrs is rank-major like grad_ptrs.
+ */
+int ga_average_host(ga_ctx *ctx, void *const *host_ptrs, const int64_t *numel, int n_tensors,
+                    void *stream, int variant);
+
+/*
+ * Call on `stream` before writing into ga_send_ptr() if the previous call on this context was a
+ * tensor-list call (ga_average / ga_allreduce_tensors): those let their peers finish reading this
+ * rank's bucket lazily, and this enqueues the wait for them.  A no-op after bucket-direct calls.
+ */
+int ga_bucket_acquire(ga_ctx *ctx, void *stream);
+
+/* Device pointers of local rank `local_rank`'s bucket (what peers read) and result region. */
+void *ga_send_ptr(ga_ctx *ctx, int local_rank);
+void *ga_recv_ptr(ga_ctx *ctx, int local_rank);
+
+/* Byte offset of tensor `i` inside the bucket for the given element counts (segments are
+ * padded to 2 KiB tiles); with i == n_tensors returns the total bytes used. */
+int64_t ga_bucket_offset(const int64_t *numel, int n_tensors, int i);
+
+/* world size / first hosted rank / number of hosted ranks / capacity in bytes */
+int ga_world(const ga_ctx *ctx);
+int ga_rank(const ga_ctx *ctx);
+int ga_n_local(const ga_ctx *ctx);
+size_t ga_capacity(const ga_ctx *ctx);
+
+/* What AUTO resolves to for `nbytes` (GA_VARIANT_ONESHOT or GA_VARIANT_TWOSHOT). */
+int ga_pick_variant(const ga_ctx *ctx, size_t nbytes);
+
+/* Kernels launched by this context so far (for bench.py's gpu_launches). */
+uint64_t ga_launch_count(const ga_ctx *ctx);
+
+/* Grid the last launch used: blocks per rank and threads per block. */
+int ga_last_grid(const ga_ctx *ctx, int *blocks, int *threads);
+
+int ga_set_option(ga_ctx *ctx, int option, int64_t value);
+
+/* 0, or GA_ETIMEOUT once a kernel of this context gave up waiting for a peer (the context is
+ * then unusable).  Reads a host-mapped word; call after synchronising the stream. */
+int ga_status(ga_ctx *ctx);
+
+/* Frees everything.  Every rank must have finished its last call (barrier first). */
+int ga_destroy(ga_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRADAVG_H_ */

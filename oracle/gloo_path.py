@@ -1,0 +1,134 @@
+"""The reference hot path on its own CPU backend (TEST INFRASTRUCTURE).
+
+`average_gradients_ref` restates `/root/reference/mnist/main.py:122-127` statement for
+statement on `torch.distributed`; `toy_allreduce_ref` restates `/root/reference/toy/main.py:15-20`.
+`run_world` starts `world` CPU processes on 127.0.0.1 with the gloo backend, the way the
+reference READMEs do by hand (`mnist/README.md:18-33`), and returns every rank's result.
+
+The arithmetic below `all_reduce` is gloo's, statically linked into the installed torch wheel
+(`third_party/gloo/gloo/allreduce.cc`; effective pin: torch 2.11.0+cu128 of this image -- the
+reference itself pins only `pytorch>=0.4.0`, README.md:5).  This file is also what
+`bench.py` times as `cpu_baseline` (kind "port") and under `--impl reference`.
+"""
+import os
+import socket
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def average_gradients_ref(params, world_size=None):
+    """mnist/main.py:122-127."""
+    if world_size is None:
+        world_size = dist.get_world_size()            # :123
+    for p in params:                                  # :125
+        dist.all_reduce(p.grad.data, op=dist.ReduceOp.SUM)   # :126 (reduce_op is the old alias)
+        p.grad.data /= float(world_size)              # :127
+
+
+def toy_allreduce_ref(value, world_size):
+    """toy/main.py:15-20: new group of all ranks, IntTensor([value]), all_reduce SUM."""
+    group = dist.new_group(ranks=list(range(world_size)))   # :15-16
+    tensor = torch.IntTensor([value])                        # :19
+    dist.all_reduce(tensor, op=dist.ReduceOp.SUM, group=group)  # :20
+    return float(tensor)                                     # :23
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, fn, args, out_dir, threads):
+    torch.set_num_threads(threads)
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    try:
+        res = fn(rank, world, *args)
+        if res is not None:
+            torch.save(res, os.path.join(out_dir, "rank%d.pt" % rank))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def run_world(world, fn, args=(), threads=1):
+    """Run fn(rank, world, *args) on `world` gloo CPU ranks; returns [result of rank 0, 1, ...]."""
+    import tempfile
+    port = free_port()
+    with tempfile.TemporaryDirectory() as d:
+        mp.spawn(_worker, args=(world, port, fn, args, d, threads), nprocs=world, join=True)
+        out = []
+        for r in range(world):
+            f = os.path.join(d, "rank%d.pt" % r)
+            out.append(torch.load(f, weights_only=False) if os.path.exists(f) else None)
+    return out
+
+
+class _P:  # minimal stand-in for a parameter: only `.grad.data` is touched by the path
+    def __init__(self, g):
+        self.grad = g
+
+
+def _avg_job(rank, world, shapes, positive, base_seed):
+    from .gradient_sets import seeded_grads, seeded_positive_grads
+    grads = (seeded_positive_grads if positive else seeded_grads)(shapes, rank, base_seed)
+    params = [_P(g) for g in grads]
+    average_gradients_ref(params, world)
+    return [p.grad.numpy() for p in params]
+
+
+def gloo_average(world, shapes, positive=False, base_seed=1234):
+    """Average the seeded gradient set over `world` gloo ranks; returns rank 0's tensors and
+    asserts that every rank ended with identical bytes."""
+    res = run_world(world, _avg_job, (shapes, positive, base_seed))
+    for r in range(1, world):
+        for a, b in zip(res[0], res[r]):
+            assert a.tobytes() == b.tobytes(), "gloo ranks disagree"
+    return res[0]
+
+
+def _flat_job(rank, world, numel, iters, warmup, base_seed):
+    g = torch.Generator().manual_seed(base_seed + rank)
+    buf = torch.randn(numel, generator=g, dtype=torch.float32)
+    p = [_P(buf)]
+    times = []
+    for i in range(warmup + iters):
+        dist.barrier()
+        t0 = time.perf_counter()
+        average_gradients_ref(p, world)
+        t1 = time.perf_counter()
+        t = torch.tensor([t1 - t0], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if i >= warmup:
+            times.append(float(t))
+    return times
+
+
+def time_flat_average(world, numel, iters, warmup=1, threads=1, base_seed=1234):
+    """Wall-clock seconds per reference-style averaging of one flat fp32 buffer (max over
+    ranks per iteration), BASELINE.md section 4."""
+    return run_world(world, _flat_job, (numel, iters, warmup, base_seed), threads=threads)[0]
+
+
+def _set_job(rank, world, shapes, iters, warmup, base_seed):
+    from .gradient_sets import seeded_grads
+    params = [_P(g) for g in seeded_grads(shapes, rank, base_seed)]
+    times = []
+    for i in range(warmup + iters):
+        dist.barrier()
+        t0 = time.perf_counter()
+        average_gradients_ref(params, world)
+        t1 = time.perf_counter()
+        t = torch.tensor([t1 - t0], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if i >= warmup:
+            times.append(float(t))
+    return times
+
+
+def time_set_average(world, shapes, iters, warmup=1, threads=1, base_seed=1234):
+    return run_world(world, _set_job, (shapes, iters, warmup, base_seed), threads=threads)[0]

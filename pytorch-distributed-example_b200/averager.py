@@ -1,0 +1,313 @@
+"""Host side of the hot path: owns the C context, exchanges the IPC handles once, and turns a
+parameter list into the pointer table the kernel reads (mirrors `Trainer.average_gradients`,
+`/root/reference/mnist/main.py:122-127`)."""
+import ctypes
+import threading
+
+import torch
+
+from . import _lib
+from ._lib import GradAvgError, check, load_library
+
+AUTO, ONESHOT, TWOSHOT = _lib.VARIANT_AUTO, _lib.VARIANT_ONESHOT, _lib.VARIANT_TWOSHOT
+_VARIANTS = {"auto": AUTO, "oneshot": ONESHOT, "1shot": ONESHOT, "twoshot": TWOSHOT, "2shot": TWOSHOT,
+             AUTO: AUTO, ONESHOT: ONESHOT, TWOSHOT: TWOSHOT, None: AUTO}
+
+
+def _tiles(numel):
+    return (numel * 4 + _lib.TILE_BYTES - 1) // _lib.TILE_BYTES
+
+
+def bucket_bytes(numels):
+    """Bytes a gradient set occupies in the bucket (each tensor padded to a 2 KiB tile)."""
+    return sum(_tiles(n) for n in numels) * _lib.TILE_BYTES
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise GradAvgError(_lib.GA_ESTATE, "no CUDA device: this path has no CPU fallback")
+
+
+class GradAverager:
+    """One per process (one rank per GPU), or one hosting all ranks on a single GPU.
+
+    world_size/rank default to the initialised `torch.distributed` default group -- the one the
+    reference script creates at `mnist/main.py:199-203` -- which is also what carries the 64-byte
+    CUDA-IPC handles, once.  `local_world=W` hosts W ranks in this process on one device instead
+    (no process group needed).
+    """
+
+    def __init__(self, world_size=None, rank=None, device=None, capacity_bytes=None, group=None,
+                 local_world=None, variant=None):
+        self._lib = load_library()
+        self._ctx = None
+        self._lock = threading.Lock()          # calls on one context are serialised (header contract)
+        self._group = group
+        self._variant = _VARIANTS[variant]
+        self._capacity = capacity_bytes
+        self._local = int(local_world) if local_world else 0
+        if self._local:
+            self.world_size, self.rank = self._local, 0
+        else:
+            import torch.distributed as dist
+            self.world_size = int(world_size if world_size is not None else dist.get_world_size(group))
+            self.rank = int(rank if rank is not None else dist.get_rank(group))
+        if not 1 <= self.world_size <= _lib.MAX_WORLD:
+            raise GradAvgError(_lib.GA_EINVAL, "world_size %d outside 1..%d" % (self.world_size, _lib.MAX_WORLD))
+        self._device = device
+        self._ptr_cache = {}
+        if capacity_bytes:
+            self._create(capacity_bytes)
+
+    # -- context lifetime -------------------------------------------------------------------
+    @property
+    def n_local(self):
+        return self._local or 1
+
+    @property
+    def device(self):
+        if self._device is None:
+            _require_cuda()
+            self._device = torch.cuda.current_device()
+        return torch.device("cuda", self._device) if isinstance(self._device, int) else torch.device(self._device)
+
+    def _create(self, capacity_bytes):
+        _require_cuda()
+        dev = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        ctx = ctypes.c_void_p()
+        if self._local:
+            check(self._lib.ga_create_local(self.world_size, dev, int(capacity_bytes), ctypes.byref(ctx)))
+        else:
+            check(self._lib.ga_create(self.rank, self.world_size, dev, int(capacity_bytes), ctypes.byref(ctx)))
+        self._ctx = ctx
+        self._capacity = int(self._lib.ga_capacity(ctx))
+        if not self._local:
+            self._exchange_handles()
+
+    def _exchange_handles(self):
+        """all_gather of the 64-byte cudaIpcMemHandle over the script's own process group."""
+        import torch.distributed as dist
+        mine = ctypes.create_string_buffer(_lib.IPC_HANDLE_BYTES)
+        check(self._lib.ga_export_handle(self._ctx, mine))
+        if self.world_size == 1:
+            check(self._lib.ga_open_peers(self._ctx, mine.raw))
+            return
+        backend = dist.get_backend(self._group)
+        dev = self.device if "nccl" in str(backend) else torch.device("cpu")
+        t = torch.frombuffer(bytearray(mine.raw), dtype=torch.uint8).to(dev)
+        out = [torch.empty_like(t) for _ in range(self.world_size)]
+        dist.all_gather(out, t, group=self._group)
+        blob = b"".join(bytes(o.cpu().numpy().tobytes()) for o in out)
+        check(self._lib.ga_open_peers(self._ctx, blob))
+        dist.barrier(group=self._group)      # nobody signals into a pad that is not mapped yet
+
+    def _ensure(self, need_bytes):
+        if self._ctx is not None and need_bytes <= self._capacity:
+            return
+        if self._ctx is not None:
+            # Every rank sees the same sizes, so every rank takes this branch in the same call.
+            self.close()
+        self._create(max(need_bytes, 1 << 20))
+
+    def close(self):
+        if self._ctx is not None:
+            if torch.cuda.is_available():
+                torch.cuda.synchronize()
+            if not self._local and self.world_size > 1:
+                import torch.distributed as dist
+                if dist.is_initialized():
+                    dist.barrier(group=self._group)   # peers may still be reading my bucket
+            self._lib.ga_destroy(self._ctx)
+            self._ctx = None
+            self._ptr_cache.clear()
+
+    def __del__(self):
+        try:
+            if self._ctx is not None:
+                self._lib.ga_destroy(self._ctx)
+                self._ctx = None
+        except Exception:
+            pass
+
+    # -- the hot path -----------------------------------------------------------------------
+    @staticmethod
+    def _grads_of(params):
+        if isinstance(params, torch.nn.Module):
+            params = params.parameters()
+        grads = []
+        for p in params:
+            g = p.grad
+            if g is None:
+                # the reference would raise AttributeError on `None.data` (mnist/main.py:126)
+                raise AttributeError("parameter without .grad: 'NoneType' object has no attribute 'data'")
+            grads.append(g.data)
+        return grads
+
+    def _table(self, per_rank_tensors, dtype):
+        n = len(per_rank_tensors[0])
+        key = (len(per_rank_tensors), n)
+        arrs = self._ptr_cache.get(key)
+        if arrs is None:
+            arrs = ((ctypes.c_void_p * (n * len(per_rank_tensors)))(), (ctypes.c_int64 * n)())
+            self._ptr_cache[key] = arrs
+        ptrs, numel = arrs
+        dev = self.device
+        k = 0
+        for tensors in per_rank_tensors:
+            if len(tensors) != n:
+                raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different tensor counts")
+            for i, t in enumerate(tensors):
+                if t.dtype != dtype or not t.is_cuda or t.device != dev:
+                    raise GradAvgError(_lib.GA_EINVAL, "tensor %d: need %s on %s, got %s on %s (no CPU fallback)"
+                                       % (i, dtype, dev, t.dtype, t.device))
+                if not t.is_contiguous():
+                    raise GradAvgError(_lib.GA_EINVAL, "tensor %d is not contiguous" % i)
+                ptrs[k] = t.data_ptr()
+                k += 1
+        for i, t in enumerate(per_rank_tensors[0]):
+            numel[i] = t.numel()
+        return ptrs, numel, n
+
+    def _run_tensors(self, per_rank_tensors, op, dtype, variant):
+        with self._lock:
+            numels = [t.numel() for t in per_rank_tensors[0]]
+            self._ensure(bucket_bytes(numels))
+            ptrs, numel, n = self._table(per_rank_tensors, dtype)
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            v = self._variant if variant is None else _VARIANTS[variant]
+            check(self._lib.ga_allreduce_tensors(self._ctx, ptrs, numel, n, op, ctypes.c_void_p(stream), v))
+
+    def average_gradients(self, params, variant=None):
+        """`Trainer.average_gradients` (mnist/main.py:122-127) for one rank: every `p.grad` is
+        replaced IN PLACE by the rank-order sum over all ranks divided by float(world_size).
+        Stream-ordered on torch's current stream; returns after the launch."""
+        self._run_tensors([self._grads_of(params)], _lib.OP_F32_AVG, torch.float32, variant)
+
+    def average_gradients_local(self, per_rank_params, variant=None):
+        """Same for a local world: one parameter list per hosted rank, rank order."""
+        if len(per_rank_params) != self.n_local:
+            raise GradAvgError(_lib.GA_EINVAL, "need %d parameter lists" % self.n_local)
+        self._run_tensors([self._grads_of(p) for p in per_rank_params], _lib.OP_F32_AVG, torch.float32, variant)
+
+    def all_reduce_(self, tensors, average=False, variant=None):
+        """In-place SUM (or average) of a list of CUDA tensors (fp32 or int32), one list per hosted
+        rank -- the op under `distributed.all_reduce(t, op=SUM)` (mnist/main.py:126, toy/main.py:20)."""
+        if torch.is_tensor(tensors):
+            tensors = [[tensors]]
+        elif tensors and torch.is_tensor(tensors[0]):
+            tensors = [list(tensors)]
+        dtype = tensors[0][0].dtype
+        if dtype == torch.float32:
+            op = _lib.OP_F32_AVG if average else _lib.OP_F32_SUM
+        elif dtype == torch.int32 and not average:
+            op = _lib.OP_I32_SUM
+        else:
+            raise GradAvgError(_lib.GA_EINVAL, "unsupported dtype/op: %s average=%s" % (dtype, average))
+        self._run_tensors(tensors, op, dtype, variant)
+
+    def average_host(self, per_rank_host_tensors, variant=None):
+        """Host-buffer form (`ga_average_host`): pinned CPU fp32 tensors, H2D -> reduce -> D2H,
+        stream-ordered; the caller synchronises the stream before reading the tensors."""
+        if per_rank_host_tensors and torch.is_tensor(per_rank_host_tensors[0]):
+            per_rank_host_tensors = [list(per_rank_host_tensors)]
+        with self._lock:
+            numels = [t.numel() for t in per_rank_host_tensors[0]]
+            self._ensure(bucket_bytes(numels))
+            n = len(numels)
+            ptrs = (ctypes.c_void_p * (n * len(per_rank_host_tensors)))()
+            k = 0
+            for ts in per_rank_host_tensors:
+                for t in ts:
+                    if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+                        raise GradAvgError(_lib.GA_EINVAL, "average_host needs contiguous CPU fp32 tensors")
+                    ptrs[k] = t.data_ptr()
+                    k += 1
+            numel = (ctypes.c_int64 * n)(*numels)
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            v = self._variant if variant is None else _VARIANTS[variant]
+            check(self._lib.ga_average_host(self._ctx, ptrs, numel, n, ctypes.c_void_p(stream), v))
+
+    # -- bucket-direct form (size sweep, NCCL comparison) -------------------------------------
+    def reserve(self, nbytes):
+        with self._lock:
+            self._ensure(int(nbytes))
+
+    def _view(self, ptr, nbytes, dtype):
+        n = nbytes // 4
+
+        class _Holder:
+            pass
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4" if dtype == torch.float32 else "<i4",
+                                      "data": (int(ptr), False), "version": 2}
+        return torch.as_tensor(h, device=self.device)
+
+    def send_view(self, nbytes=None, local_rank=0, dtype=torch.float32):
+        """Tensor aliasing this rank's bucket (what the peers read)."""
+        return self._view(self._lib.ga_send_ptr(self._ctx, local_rank), nbytes or self._capacity, dtype)
+
+    def recv_view(self, nbytes=None, local_rank=0, dtype=torch.float32):
+        """Tensor aliasing this rank's result region of the bucket-direct calls."""
+        return self._view(self._lib.ga_recv_ptr(self._ctx, local_rank), nbytes or self._capacity, dtype)
+
+    def bucket_acquire(self):
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with self._lock:
+            check(self._lib.ga_bucket_acquire(self._ctx, ctypes.c_void_p(stream)))
+
+    def allreduce_bucket(self, nbytes, op=_lib.OP_F32_AVG, variant=None):
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        v = self._variant if variant is None else _VARIANTS[variant]
+        with self._lock:
+            check(self._lib.ga_allreduce_bucket(self._ctx, int(nbytes), op, ctypes.c_void_p(stream), v))
+
+    # -- introspection ----------------------------------------------------------------------
+    def set_option(self, option, value):
+        check(self._lib.ga_set_option(self._ctx, option, int(value)))
+
+    def pick_variant(self, nbytes):
+        return self._lib.ga_pick_variant(self._ctx, int(nbytes))
+
+    @property
+    def launch_count(self):
+        return int(self._lib.ga_launch_count(self._ctx)) if self._ctx is not None else 0
+
+    @property
+    def last_grid(self):
+        b, t = ctypes.c_int(), ctypes.c_int()
+        check(self._lib.ga_last_grid(self._ctx, ctypes.byref(b), ctypes.byref(t)))
+        return b.value, t.value
+
+    @property
+    def capacity(self):
+        return self._capacity or 0
+
+    def check_status(self):
+        """Raises GradAvgError(GA_ETIMEOUT) if a kernel gave up on a peer. Synchronises first."""
+        torch.cuda.synchronize(self.device)
+        check(self._lib.ga_status(self._ctx))
+
+
+_default = None
+
+
+def default_averager():
+    """The process-wide averager bound to the default process group, created on first use and
+    sized from the first parameter list it sees."""
+    global _default
+    if _default is None:
+        _default = GradAverager()
+    return _default
+
+
+def reset_default_averager():
+    global _default
+    if _default is not None:
+        _default.close()
+    _default = None
+
+
+def average_gradients(params, variant=None):
+    """Drop-in body for `Trainer.average_gradients` (mnist/main.py:122-127): accepts the module
+    or its `parameters()`."""
+    default_averager().average_gradients(params, variant=variant)

@@ -1,0 +1,872 @@
+// gradavg.cu -- sm_100a kernels + C ABI of libgradavg.so (declared in include/gradavg.h).
+//
+// The one hot path of dblakely/pytorch-distributed-example, /root/reference/mnist/main.py:122-127
+// (all_reduce(SUM) of every p.grad, then /= float(world_size)) and toy/main.py:19-20, as ONE
+// fused kernel per call:
+//
+//   pack   gather the per-parameter gradients into this rank's flat bucket (16-byte vectors,
+//          every tensor padded to a 2 KiB tile so a warp-tile never straddles two tensors)
+//   flag   per-block release/acquire flags written straight into the peers' memory
+//   reduce read the peers' buckets over NVLink (plain ld.global on CUDA-IPC mapped pointers),
+//          add in rank order, divide by (float)world  -- one-shot: every rank reads everything;
+//          two-shot: rank r reduces shard r in place, then every rank pulls the other shards
+//   unpack write the result straight into the gradient tensors (no second pass)
+//
+// Nothing here is a contraction, so no tensor cores; the kernel is HBM-bound on one GPU and
+// NVLink-bound across GPUs.  Build: see __graft_entry__.build().
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/gradavg.h"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// constants and device-visible structures
+// ------------------------------------------------------------------------------------------
+constexpr int kMaxWorld = GA_MAX_WORLD;
+constexpr int kTileVecs = 128;                 // 16-byte vectors per warp tile
+constexpr int kTileBytes = kTileVecs * 16;     // 2 KiB
+constexpr int kTileElems = kTileVecs * 4;      // 512 32-bit elements
+constexpr int kLaneVecs = kTileVecs / 32;      // 4 vectors per lane per tile
+constexpr int kThreads = 512;                  // 16 warps per block
+constexpr int kMaxBlocks = 1024;               // flag rows per rank
+constexpr int kInlineSegs = 128;               // pointer-table entries carried in kernel params
+constexpr int kSegRing = 4;                    // staging slots for larger pointer tables
+
+typedef uint4 Vec;
+
+struct Seg {               // one gradient tensor of one rank
+    const void *ptr;       // device pointer (re-read every call)
+    uint32_t start_tile;   // first bucket tile of this tensor
+    uint32_t numel;        // 32-bit elements
+};
+
+struct Pad {                                    // head of every rank's IPC allocation
+    uint32_t ready[kMaxBlocks][kMaxWorld];      // [block][src rank]: src packed its tiles (epoch)
+    uint32_t mid[kMaxBlocks][kMaxWorld];        // [block][src rank]: src reduced its shard (epoch)
+    uint32_t done[kMaxWorld];                   // [src rank]: src finished reading my bucket (epoch)
+    uint32_t finished_blocks;                   // local block counter of the running launch
+    uint32_t reserved[23];
+};
+constexpr size_t kPadBytes = (sizeof(Pad) + 4095) / 4096 * 4096;
+
+struct Params {
+    void *send[kMaxWorld];      // every rank's bucket, by global rank (peer-mapped)
+    Pad *pad[kMaxWorld];        // every rank's flag pad, by global rank (peer-mapped)
+    void *recv[kMaxWorld];      // result regions of the hosted ranks, by local index
+    const Seg *dev_segs;        // [n_local][n_seg], or nullptr -> inline_segs
+    int *status;                // host-mapped error word
+    unsigned long long timeout_ns;
+    uint32_t n_seg;
+    uint32_t total_tiles;
+    uint32_t shard_tiles;       // two-shot: tiles per rank shard
+    uint32_t epoch;
+    int rank_base;
+    int direct;                 // 1: bucket-direct (no pack, result -> recv)
+    Seg inline_segs[kInlineSegs];
+};
+
+// ------------------------------------------------------------------------------------------
+// element operations
+// ------------------------------------------------------------------------------------------
+template <int OP> struct ElemOp;
+template <> struct ElemOp<GA_OP_F32_AVG> {
+    // __fadd_rn / __fdiv_rn: single IEEE binary32 operations, never contracted or replaced by
+    // a reciprocal multiply (x/3.0f != x*(1/3.0f)).
+    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) {
+        return __float_as_uint(__fadd_rn(__uint_as_float(a), __uint_as_float(b)));
+    }
+    static __device__ __forceinline__ uint32_t fin(uint32_t a, float w) {
+        return __float_as_uint(__fdiv_rn(__uint_as_float(a), w));
+    }
+};
+template <> struct ElemOp<GA_OP_F32_SUM> {
+    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) {
+        return __float_as_uint(__fadd_rn(__uint_as_float(a), __uint_as_float(b)));
+    }
+    static __device__ __forceinline__ uint32_t fin(uint32_t a, float) { return a; }
+};
+template <> struct ElemOp<GA_OP_I32_SUM> {
+    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) { return a + b; }
+    static __device__ __forceinline__ uint32_t fin(uint32_t a, float) { return a; }
+};
+
+// ------------------------------------------------------------------------------------------
+// flags
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Spin until *flag has reached `target` (wrap-safe).  Returns false on timeout.
+__device__ __forceinline__ bool spin_until(const uint32_t *flag, uint32_t target, unsigned long long timeout_ns) {
+    unsigned long long t0 = 0;
+    uint32_t spins = 0;
+    while ((int32_t)(ld_relaxed_sys(flag) - target) < 0) {
+        if ((++spins & 1023u) == 0 && timeout_ns) {
+            unsigned long long now = global_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > timeout_ns) return false;
+        }
+    }
+    return true;
+}
+
+// Block-wide: threads 0..W-1 each wait for one source rank's flag, then everyone syncs.
+// Returns false (for the whole block) if any wait timed out.
+template <int W>
+__device__ __forceinline__ bool wait_flags(const uint32_t *row, uint32_t target, const Params &p, int *s_abort) {
+    if (threadIdx.x < W) {
+        if (!spin_until(row + threadIdx.x, target, p.timeout_ns)) {
+            *s_abort = 1;
+            *(volatile int *)p.status = GA_ETIMEOUT;
+        }
+        asm volatile("fence.acq_rel.sys;" ::: "memory");   // acquire: peers' data before our loads of it
+    }
+    __syncthreads();
+    return *s_abort == 0;
+}
+
+// Block-wide: everything this block wrote so far becomes visible, then flag `col` of row
+// `row_off` is raised in every rank's pad.
+template <int W>
+__device__ __forceinline__ void raise_flags(const Params &p, size_t word_off, uint32_t value) {
+    __syncthreads();
+    if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + word_off, value);
+}
+
+// ------------------------------------------------------------------------------------------
+// tile movers (one warp moves one 2 KiB tile; lane l owns vectors l, l+32, l+64, l+96)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ int find_seg(const Seg *segs, int n, uint32_t tile) {
+    int lo = 0, hi = n - 1;          // largest s with segs[s].start_tile <= tile
+    while (lo < hi) {
+        int m = (lo + hi + 1) >> 1;
+        if (segs[m].start_tile <= tile) lo = m; else hi = m - 1;
+    }
+    return lo;
+}
+
+// gradient tensor -> registers (zero fill past the end of the tensor)
+__device__ __forceinline__ void load_grad_tile(const Seg &sg, uint32_t tile, int lane, Vec (&v)[kLaneVecs]) {
+    const uint32_t *src = (const uint32_t *)sg.ptr;
+    const size_t n = sg.numel;
+    const size_t base = (size_t)(tile - sg.start_tile) * kTileElems;
+    const bool aligned = (((uintptr_t)src) & 15) == 0;
+#pragma unroll
+    for (int u = 0; u < kLaneVecs; ++u) {
+        const size_t e = base + (size_t)(u * 32 + lane) * 4;
+        if (aligned && e + 4 <= n) {
+            v[u] = __ldcs((const Vec *)(src + e));
+        } else {
+            v[u].x = e + 0 < n ? __ldcs(src + e + 0) : 0u;
+            v[u].y = e + 1 < n ? __ldcs(src + e + 1) : 0u;
+            v[u].z = e + 2 < n ? __ldcs(src + e + 2) : 0u;
+            v[u].w = e + 3 < n ? __ldcs(src + e + 3) : 0u;
+        }
+    }
+}
+
+// registers -> gradient tensor (elements past the end are dropped)
+template <int NV>
+__device__ __forceinline__ void store_grad_vecs(const Seg &sg, uint32_t tile, int lane, int u0, const Vec (&v)[NV]) {
+    uint32_t *dst = (uint32_t *)sg.ptr;
+    const size_t n = sg.numel;
+    const size_t base = (size_t)(tile - sg.start_tile) * kTileElems;
+    const bool aligned = (((uintptr_t)dst) & 15) == 0;
+#pragma unroll
+    for (int u = 0; u < NV; ++u) {
+        const size_t e = base + (size_t)((u0 + u) * 32 + lane) * 4;
+        if (aligned && e + 4 <= n) {
+            *(Vec *)(dst + e) = v[u];
+        } else {
+            if (e + 0 < n) dst[e + 0] = v[u].x;
+            if (e + 1 < n) dst[e + 1] = v[u].y;
+            if (e + 2 < n) dst[e + 2] = v[u].z;
+            if (e + 3 < n) dst[e + 3] = v[u].w;
+        }
+    }
+}
+
+// Where a finished tile goes: the gradient tensors (fused unpack) or the result region.
+struct Sink {
+    const Seg *segs;   // this rank's pointer table (nullptr in bucket-direct mode)
+    int n_seg;
+    Vec *recv;         // bucket-direct destination
+};
+
+template <int NV>
+__device__ __forceinline__ void sink_store(const Sink &s, const Seg *sg, uint32_t tile, int lane, int u0, const Vec (&v)[NV]) {
+    if (sg) {
+        store_grad_vecs<NV>(*sg, tile, lane, u0, v);
+    } else {
+        Vec *d = s.recv + (size_t)tile * kTileVecs + u0 * 32 + lane;
+#pragma unroll
+        for (int u = 0; u < NV; ++u) d[u * 32] = v[u];
+    }
+}
+
+// Vectors per lane fetched from EVERY rank before the adds start: W * kBatch loads in flight
+// per thread, capped so that the kernel stays within 64 registers (2 blocks of 512 per SM).
+template <int W> struct Batch { static constexpr int value = W <= 2 ? 4 : (W <= 4 ? 2 : 1); };
+
+// Reduce one tile from all W buckets in rank order, divide, store to `own` (two-shot in-place
+// shard, may be nullptr) and to the sink.
+template <int W, int OP>
+__device__ __forceinline__ void reduce_tile(const Params &p, uint32_t tile, int lane, float wf,
+                                            Vec *own, const Sink &sink, const Seg *sg) {
+    constexpr int NB = Batch<W>::value;
+    const size_t off = (size_t)tile * kTileVecs + lane;
+#pragma unroll
+    for (int u0 = 0; u0 < kLaneVecs; u0 += NB) {
+        Vec v[W][NB];
+#pragma unroll
+        for (int r = 0; r < W; ++r)
+#pragma unroll
+            for (int u = 0; u < NB; ++u)
+                v[r][u] = __ldcg((const Vec *)p.send[r] + off + (u0 + u) * 32);
+        Vec acc[NB];
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+            acc[u] = v[0][u];
+#pragma unroll
+            for (int r = 1; r < W; ++r) {          // ((g0 + g1) + g2) + ...
+                acc[u].x = ElemOp<OP>::add(acc[u].x, v[r][u].x);
+                acc[u].y = ElemOp<OP>::add(acc[u].y, v[r][u].y);
+                acc[u].z = ElemOp<OP>::add(acc[u].z, v[r][u].z);
+                acc[u].w = ElemOp<OP>::add(acc[u].w, v[r][u].w);
+            }
+            acc[u].x = ElemOp<OP>::fin(acc[u].x, wf);
+            acc[u].y = ElemOp<OP>::fin(acc[u].y, wf);
+            acc[u].z = ElemOp<OP>::fin(acc[u].z, wf);
+            acc[u].w = ElemOp<OP>::fin(acc[u].w, wf);
+        }
+        if (own) {
+#pragma unroll
+            for (int u = 0; u < NB; ++u) __stcg(own + off + (u0 + u) * 32, acc[u]);
+        }
+        sink_store<NB>(sink, sg, tile, lane, u0, acc);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------
+// grid = (blocks per rank, hosted ranks).  Block b of rank r only ever waits for block b of
+// the other ranks, and only touches bucket tiles of its own "column": tile slot
+// i = (k * gridDim.x + b) * warps + warp, for k = 0, 1, ...  In the one-shot variant slot i is
+// bucket tile i; in the two-shot variant it is tile i of EVERY shard (j * shard_tiles + i).
+// That makes the producer of every byte a block of the same index b, so a row of per-block
+// flags is the only synchronisation.
+template <int W, int VARIANT, int OP>
+__global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_constant__ Params p) {
+    __shared__ int s_abort;
+    __shared__ int s_last;
+    const int ly = blockIdx.y;
+    const int r = p.rank_base + ly;
+    const int b = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpb = blockDim.x >> 5;
+    const uint32_t stride = gridDim.x * wpb;
+    const uint32_t first = b * wpb + warp;
+    const uint32_t T = p.total_tiles;
+    const float wf = (float)W;
+
+    Pad *mypad = p.pad[r];
+    Vec *mysend = (Vec *)p.send[r];
+    Sink sink;
+    sink.n_seg = (int)p.n_seg;
+    sink.segs = p.direct ? nullptr : (p.dev_segs ? p.dev_segs : p.inline_segs) + (size_t)ly * p.n_seg;
+    sink.recv = (Vec *)p.recv[ly];
+
+    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
+    __syncthreads();
+
+    // (0) The previous call's readers must be done with my bucket before pack overwrites it.
+    //     (Bucket-direct calls end with this wait instead, see the bottom.)
+    if (!p.direct) {
+        if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+    }
+
+    // (1) pack: gradient tensors -> my bucket
+    if (!p.direct) {
+        if (VARIANT == GA_VARIANT_ONESHOT) {
+            for (uint32_t t = first; t < T; t += stride) {
+                const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+                Vec v[kLaneVecs];
+                load_grad_tile(sg, t, lane, v);
+#pragma unroll
+                for (int u = 0; u < kLaneVecs; ++u) __stcg(mysend + (size_t)t * kTileVecs + u * 32 + lane, v[u]);
+            }
+        } else {
+            for (uint32_t i = first; i < p.shard_tiles; i += stride) {
+                for (int j = 0; j < W; ++j) {
+                    const uint32_t t = j * p.shard_tiles + i;
+                    if (t >= T) break;
+                    const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+                    Vec v[kLaneVecs];
+                    load_grad_tile(sg, t, lane, v);
+#pragma unroll
+                    for (int u = 0; u < kLaneVecs; ++u) __stcg(mysend + (size_t)t * kTileVecs + u * 32 + lane, v[u]);
+                }
+            }
+        }
+    }
+
+    // (2) barrier 1: my column is packed / wait for the same column of every rank
+    const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
+    raise_flags<W>(p, ready_off, p.epoch);
+    if (!wait_flags<W>(mypad->ready[b], p.epoch, p, &s_abort)) return;
+
+    if (VARIANT == GA_VARIANT_ONESHOT) {
+        // (3) every rank reduces every tile and writes its own copy of the result
+        for (uint32_t t = first; t < T; t += stride) {
+            const Seg *sg = nullptr;
+            Seg sgv;
+            if (sink.segs) { sgv = sink.segs[find_seg(sink.segs, sink.n_seg, t)]; sg = &sgv; }
+            reduce_tile<W, OP>(p, t, lane, wf, nullptr, sink, sg);
+        }
+    } else {
+        // (3) reduce-scatter: rank r reduces shard r in place in its bucket (+ its own copy out)
+        for (uint32_t i = first; i < p.shard_tiles; i += stride) {
+            const uint32_t t = r * p.shard_tiles + i;
+            if (t >= T) break;
+            const Seg *sg = nullptr;
+            Seg sgv;
+            if (sink.segs) { sgv = sink.segs[find_seg(sink.segs, sink.n_seg, t)]; sg = &sgv; }
+            reduce_tile<W, OP>(p, t, lane, wf, mysend, sink, sg);
+        }
+        // (4) barrier 2: shard column reduced everywhere
+        const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
+        raise_flags<W>(p, mid_off, p.epoch);
+        if (!wait_flags<W>(mypad->mid[b], p.epoch, p, &s_abort)) return;
+        // (5) all-gather: pull the other ranks' reduced shards, starting with the next rank so
+        //     that at any moment the W ranks read from W different sources
+        for (uint32_t i = first; i < p.shard_tiles; i += stride) {
+#pragma unroll 1
+            for (int jj = 1; jj < W; ++jj) {
+                const int j = (r + jj) % W;
+                const uint32_t t = j * p.shard_tiles + i;
+                if (t >= T) continue;
+                const Seg *sg = nullptr;
+                Seg sgv;
+                if (sink.segs) { sgv = sink.segs[find_seg(sink.segs, sink.n_seg, t)]; sg = &sgv; }
+                const Vec *src = (const Vec *)p.send[j] + (size_t)t * kTileVecs + lane;
+                Vec v[kLaneVecs];
+#pragma unroll
+                for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcg(src + u * 32);
+                sink_store<kLaneVecs>(sink, sg, t, lane, 0, v);
+            }
+        }
+    }
+
+    // (6) tell every rank that this rank no longer reads their buckets (last block only)
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x == 0) mypad->finished_blocks = 0;
+        const size_t done_off = offsetof(Pad, done) / 4 + r;
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch);
+        if (p.direct) wait_flags<W>(mypad->done, p.epoch, p, &s_abort);
+    }
+}
+
+// Launched only when a bucket-direct call follows a tensor-list call: the caller is about to
+// overwrite the bucket from the host side of the stream, so every peer must have finished
+// reading it (tensor-list calls check this lazily, at the start of the NEXT kernel).
+__global__ void ga_drain_kernel(const Pad *const *pads, int n_local, int world, uint32_t epoch,
+                                unsigned long long timeout_ns, int *status) {
+    const int l = threadIdx.x / kMaxWorld, src = threadIdx.x % kMaxWorld;
+    if (l < n_local && src < world) {
+        if (!spin_until(&pads[l]->done[src], epoch, timeout_ns)) *(volatile int *)status = GA_ETIMEOUT;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                         \
+    do {                                                                                       \
+        cudaError_t e_ = (expr);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            return fail(GA_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+typedef void (*KernelFn)(Params);
+
+template <int W, int VARIANT> KernelFn pick_op(int op) {
+    return op == GA_OP_I32_SUM   ? (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_I32_SUM>
+           : op == GA_OP_F32_SUM ? (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_F32_SUM>
+                                 : (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_F32_AVG>;
+}
+template <int W> KernelFn pick_variant(int variant, int op) {
+    return variant == GA_VARIANT_TWOSHOT ? pick_op<W, GA_VARIANT_TWOSHOT>(op) : pick_op<W, GA_VARIANT_ONESHOT>(op);
+}
+KernelFn pick_kernel(int world, int variant, int op) {
+    switch (world) {
+        case 1: return pick_variant<1>(variant, op);
+        case 2: return pick_variant<2>(variant, op);
+        case 3: return pick_variant<3>(variant, op);
+        case 4: return pick_variant<4>(variant, op);
+        case 5: return pick_variant<5>(variant, op);
+        case 6: return pick_variant<6>(variant, op);
+        case 7: return pick_variant<7>(variant, op);
+        case 8: return pick_variant<8>(variant, op);
+    }
+    return nullptr;
+}
+
+}  // namespace
+
+struct ga_ctx {
+    int world, rank_base, n_local, device;
+    size_t capacity_bytes;          // per rank, multiple of kTileBytes
+    void *base[kMaxWorld];          // own allocations [Pad | bucket], by local index
+    void *recv[kMaxWorld];          // own result regions, by local index
+    void *peer_base[kMaxWorld];     // IPC-opened peer allocations, by global rank (nullptr = not opened)
+    void *send_all[kMaxWorld];      // by global rank
+    Pad *pad_all[kMaxWorld];        // by global rank
+    bool opened, broken;
+    uint32_t epoch;                 // epoch of the last launch
+    int sm_count, blocks_per_sm[2][kMaxWorld + 1];   // unused slots stay 0
+    int max_blocks_opt;
+    size_t oneshot_max_bytes;
+    unsigned long long timeout_ns;
+    int *status_host, *status_dev;
+    Seg *seg_host[kSegRing], *seg_dev[kSegRing];
+    size_t seg_cap;                 // entries per ring slot
+    cudaEvent_t seg_event[kSegRing];
+    bool seg_used[kSegRing];
+    int seg_pos;
+    uint64_t launches;
+    int last_blocks, last_threads;
+    bool last_was_tensor_call;      // previous launch checks its readers lazily (see ga_drain_kernel)
+    const Pad **own_pads_dev;       // device array of the hosted ranks' pads, for ga_drain_kernel
+};
+
+namespace {
+
+size_t tiles_for_elems(int64_t numel) { return (size_t)((numel + kTileElems - 1) / kTileElems); }
+
+int create_common(int rank_base, int n_local, int world, int device, size_t capacity_bytes, ga_ctx **out) {
+    if (!out) return fail(GA_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (world < 1 || world > kMaxWorld) return fail(GA_EINVAL, "world=%d outside 1..%d", world, kMaxWorld);
+    if (n_local < 1 || rank_base < 0 || rank_base + n_local > world)
+        return fail(GA_EINVAL, "rank=%d (+%d hosted) outside world=%d", rank_base, n_local, world);
+    if (capacity_bytes == 0) return fail(GA_EINVAL, "capacity_bytes is 0");
+    int ndev = 0;
+    CUDA_TRY(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(GA_EINVAL, "device=%d but %d CUDA devices visible", device, ndev);
+    CUDA_TRY(cudaSetDevice(device));
+
+    ga_ctx *c = (ga_ctx *)calloc(1, sizeof(ga_ctx));
+    if (!c) return fail(GA_EINVAL, "out of host memory");
+    c->world = world; c->rank_base = rank_base; c->n_local = n_local; c->device = device;
+    c->capacity_bytes = (capacity_bytes + kTileBytes - 1) / kTileBytes * kTileBytes;
+    if (c->capacity_bytes / kTileBytes > 0xffffffffull) { free(c); return fail(GA_ECAPACITY, "capacity too large"); }
+    c->oneshot_max_bytes = world <= 2 ? (size_t)-1 : (size_t)512 << 10;
+    c->timeout_ns = 30ull * 1000000000ull;
+    const char *env = getenv("GA_TIMEOUT_MS");
+    if (env) c->timeout_ns = strtoull(env, nullptr, 10) * 1000000ull;
+
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+
+    for (int l = 0; l < n_local; ++l) {
+        CUDA_TRY(cudaMalloc(&c->base[l], kPadBytes + c->capacity_bytes));
+        CUDA_TRY(cudaMemset(c->base[l], 0, kPadBytes));
+        CUDA_TRY(cudaMalloc(&c->recv[l], c->capacity_bytes));
+        c->pad_all[rank_base + l] = (Pad *)c->base[l];
+        c->send_all[rank_base + l] = (char *)c->base[l] + kPadBytes;
+    }
+    CUDA_TRY(cudaHostAlloc((void **)&c->status_host, sizeof(int), cudaHostAllocMapped));
+    *c->status_host = 0;
+    CUDA_TRY(cudaHostGetDevicePointer((void **)&c->status_dev, c->status_host, 0));
+    {
+        const Pad *own[kMaxWorld] = {};
+        for (int l = 0; l < n_local; ++l) own[l] = (const Pad *)c->base[l];
+        CUDA_TRY(cudaMalloc((void **)&c->own_pads_dev, sizeof(own)));
+        CUDA_TRY(cudaMemcpy(c->own_pads_dev, own, sizeof(own), cudaMemcpyHostToDevice));
+    }
+    CUDA_TRY(cudaDeviceSynchronize());
+    c->opened = (n_local == world);
+    *out = c;
+    return GA_OK;
+}
+
+int ensure_seg_ring(ga_ctx *c, size_t entries) {
+    if (entries <= c->seg_cap) return GA_OK;
+    size_t cap = 1024;
+    while (cap < entries) cap *= 2;
+    for (int i = 0; i < kSegRing; ++i) {
+        if (c->seg_used[i]) CUDA_TRY(cudaEventSynchronize(c->seg_event[i]));
+        if (c->seg_host[i]) CUDA_TRY(cudaFreeHost(c->seg_host[i]));
+        if (c->seg_dev[i]) CUDA_TRY(cudaFree(c->seg_dev[i]));
+        c->seg_host[i] = nullptr; c->seg_dev[i] = nullptr;
+        CUDA_TRY(cudaHostAlloc((void **)&c->seg_host[i], cap * sizeof(Seg), cudaHostAllocDefault));
+        CUDA_TRY(cudaMalloc((void **)&c->seg_dev[i], cap * sizeof(Seg)));
+        if (!c->seg_event[i]) CUDA_TRY(cudaEventCreateWithFlags(&c->seg_event[i], cudaEventDisableTiming));
+        c->seg_used[i] = false;
+    }
+    c->seg_cap = cap;
+    return GA_OK;
+}
+
+int blocks_per_sm(ga_ctx *c, KernelFn fn, int variant) {
+    int &cached = c->blocks_per_sm[variant == GA_VARIANT_TWOSHOT][c->world];
+    if (cached == 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)fn, kThreads, 0) != cudaSuccess || n < 1) n = 1;
+        cached = n;
+    }
+    return cached;
+}
+
+// Common launch path.  `segs` (n_local * n_seg entries, rank-major) is nullptr for bucket-direct.
+int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int op, void *stream, int variant, bool direct) {
+    if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
+    if (!c->opened) return fail(GA_ESTATE, "ga_open_peers has not been called");
+    if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
+    if (variant == GA_VARIANT_AUTO) variant = ga_pick_variant(c, (size_t)total_tiles * kTileBytes);
+    if (variant != GA_VARIANT_ONESHOT && variant != GA_VARIANT_TWOSHOT) return fail(GA_EINVAL, "unknown variant %d", variant);
+    if (total_tiles == 0) return GA_OK;    // nothing to average: no launch, epoch unchanged on every rank
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+
+    Params p;
+    memset(&p, 0, sizeof(p));
+    for (int r = 0; r < c->world; ++r) { p.send[r] = c->send_all[r]; p.pad[r] = c->pad_all[r]; }
+    for (int l = 0; l < c->n_local; ++l) p.recv[l] = c->recv[l];
+    p.status = c->status_dev;
+    p.timeout_ns = c->timeout_ns;
+    p.n_seg = n_seg;
+    p.total_tiles = total_tiles;
+    p.shard_tiles = (total_tiles + c->world - 1) / c->world;
+    p.epoch = c->epoch + 1;
+    p.rank_base = c->rank_base;
+    p.direct = direct ? 1 : 0;
+
+    if (segs) {
+        const size_t entries = (size_t)n_seg * c->n_local;
+        if (entries <= (size_t)kInlineSegs) {
+            memcpy(p.inline_segs, segs, entries * sizeof(Seg));
+        } else {
+            int rc = ensure_seg_ring(c, entries);
+            if (rc) return rc;
+            const int s = c->seg_pos;
+            c->seg_pos = (s + 1) % kSegRing;
+            if (c->seg_used[s]) CUDA_TRY(cudaEventSynchronize(c->seg_event[s]));
+            memcpy(c->seg_host[s], segs, entries * sizeof(Seg));
+            CUDA_TRY(cudaMemcpyAsync(c->seg_dev[s], c->seg_host[s], entries * sizeof(Seg), cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaEventRecord(c->seg_event[s], st));
+            c->seg_used[s] = true;
+            p.dev_segs = c->seg_dev[s];
+        }
+    }
+
+    KernelFn fn = pick_kernel(c->world, variant, op);
+    // Grid: one warp per tile slot, at most what is co-resident (blocks spin on peers' flags).
+    const uint32_t slots = variant == GA_VARIANT_TWOSHOT ? p.shard_tiles : total_tiles;
+    const int wpb = kThreads / 32;
+    int resident = blocks_per_sm(c, fn, variant) * c->sm_count / c->n_local;
+    if (resident > kMaxBlocks) resident = kMaxBlocks;
+    if (c->max_blocks_opt > 0 && resident > c->max_blocks_opt) resident = c->max_blocks_opt;
+    if (resident < 1) resident = 1;
+    int blocks = (int)((slots + wpb - 1) / wpb);
+    if (blocks > resident) blocks = resident;
+    if (blocks < 1) blocks = 1;
+
+    dim3 grid(blocks, c->n_local), block(kThreads);
+    void *args[] = {&p};
+    if (c->n_local > 1) {
+        // hosted ranks wait on one another inside one launch: co-residency must be guaranteed
+        CUDA_TRY(cudaLaunchCooperativeKernel((const void *)fn, grid, block, args, 0, st));
+    } else {
+        CUDA_TRY(cudaLaunchKernel((const void *)fn, grid, block, args, 0, st));
+    }
+    c->epoch += 1;
+    c->launches += 1;
+    c->last_was_tensor_call = !direct;
+    c->last_blocks = blocks;
+    c->last_threads = kThreads;
+    return GA_OK;
+}
+
+// Called before the host side of the stream overwrites the bucket (bucket-direct callers do
+// that themselves, ga_average_host does it with its H2D copies).
+int drain_if_needed(ga_ctx *c, void *stream) {
+    if (!c->last_was_tensor_call) return GA_OK;
+    CUDA_TRY(cudaSetDevice(c->device));
+    ga_drain_kernel<<<1, kMaxWorld * kMaxWorld, 0, (cudaStream_t)stream>>>(
+        c->own_pads_dev, c->n_local, c->world, c->epoch, c->timeout_ns, c->status_dev);
+    CUDA_TRY(cudaGetLastError());
+    c->launches += 1;
+    c->last_was_tensor_call = false;
+    return GA_OK;
+}
+
+// Fills rank-major Seg entries + returns total tiles.  ptrs may be nullptr (layout only).
+int build_layout(const int64_t *numel, int n_tensors, uint64_t *total_tiles) {
+    uint64_t t = 0;
+    for (int i = 0; i < n_tensors; ++i) {
+        if (numel[i] < 0) return fail(GA_EINVAL, "numel[%d] is negative", i);
+        if (numel[i] > 0xffffffffll) return fail(GA_EINVAL, "numel[%d] exceeds 2^32-1 elements", i);
+        t += tiles_for_elems(numel[i]);
+    }
+    *total_tiles = t;
+    return GA_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+const char *ga_last_error(void) { return g_err; }
+
+int ga_create(int rank, int world, int device, size_t capacity_bytes, ga_ctx **out) {
+    return create_common(rank, 1, world, device, capacity_bytes, out);
+}
+
+int ga_create_local(int world, int device, size_t capacity_bytes, ga_ctx **out) {
+    return create_common(0, world, world, device, capacity_bytes, out);
+}
+
+int ga_export_handle(ga_ctx *c, unsigned char out[GA_IPC_HANDLE_BYTES]) {
+    if (!c || !out) return fail(GA_EINVAL, "NULL argument");
+    if (c->n_local != 1) return fail(GA_ESTATE, "a local world has no handles to exchange");
+    static_assert(sizeof(cudaIpcMemHandle_t) == GA_IPC_HANDLE_BYTES, "IPC handle size");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, c->base[0]));
+    memcpy(out, &h, sizeof(h));
+    return GA_OK;
+}
+
+int ga_open_peers(ga_ctx *c, const unsigned char *handles) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (c->opened) return c->n_local == c->world ? GA_OK : fail(GA_ESTATE, "peers already opened");
+    if (!handles) return fail(GA_EINVAL, "NULL handles");
+    CUDA_TRY(cudaSetDevice(c->device));
+    for (int r = 0; r < c->world; ++r) {
+        if (r == c->rank_base) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, handles + (size_t)r * GA_IPC_HANDLE_BYTES, sizeof(h));
+        void *ptr = nullptr;
+        CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+        c->peer_base[r] = ptr;
+        c->pad_all[r] = (Pad *)ptr;
+        c->send_all[r] = (char *)ptr + kPadBytes;
+    }
+    c->opened = true;
+    return GA_OK;
+}
+
+int ga_allreduce_tensors(ga_ctx *c, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                         int op, void *stream, int variant) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (n_tensors < 0 || (n_tensors > 0 && (!ptrs || !numel))) return fail(GA_EINVAL, "bad tensor list");
+    uint64_t total = 0;
+    int rc = build_layout(numel, n_tensors, &total);
+    if (rc) return rc;
+    if (total * kTileBytes > c->capacity_bytes)
+        return fail(GA_ECAPACITY, "gradient set needs %llu bucket bytes, capacity is %zu",
+                    (unsigned long long)(total * kTileBytes), c->capacity_bytes);
+    if (total == 0) return GA_OK;
+    const size_t entries = (size_t)n_tensors * c->n_local;
+    Seg stack_segs[kInlineSegs];
+    Seg *segs = entries <= (size_t)kInlineSegs ? stack_segs : (Seg *)malloc(entries * sizeof(Seg));
+    if (!segs) return fail(GA_EINVAL, "out of host memory");
+    for (int l = 0; l < c->n_local; ++l) {
+        uint32_t start = 0;
+        for (int i = 0; i < n_tensors; ++i) {
+            Seg &s = segs[(size_t)l * n_tensors + i];
+            s.ptr = ptrs[(size_t)l * n_tensors + i];
+            s.start_tile = start;
+            s.numel = (uint32_t)numel[i];
+            if (numel[i] > 0 && !s.ptr) {
+                if (segs != stack_segs) free(segs);
+                return fail(GA_EINVAL, "pointer %d of hosted rank %d is NULL", i, l);
+            }
+            if (((uintptr_t)s.ptr & 3) != 0) {
+                if (segs != stack_segs) free(segs);
+                return fail(GA_EINVAL, "pointer %d of hosted rank %d is not 4-byte aligned", i, l);
+            }
+            start += (uint32_t)tiles_for_elems(numel[i]);
+        }
+    }
+    rc = launch(c, segs, (uint32_t)n_tensors, (uint32_t)total, op, stream, variant, false);
+    if (segs != stack_segs) free(segs);
+    return rc;
+}
+
+int ga_average(ga_ctx *c, const void *const *grad_ptrs, const int64_t *numel, int n_tensors,
+               void *stream, int variant) {
+    return ga_allreduce_tensors(c, grad_ptrs, numel, n_tensors, GA_OP_F32_AVG, stream, variant);
+}
+
+int ga_allreduce_bucket(ga_ctx *c, size_t nbytes, int op, void *stream, int variant) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (nbytes > c->capacity_bytes) return fail(GA_ECAPACITY, "%zu bytes exceed the bucket capacity %zu", nbytes, c->capacity_bytes);
+    if (nbytes % 4) return fail(GA_EINVAL, "nbytes must be a multiple of 4");
+    const uint32_t tiles = (uint32_t)((nbytes + kTileBytes - 1) / kTileBytes);
+    return launch(c, nullptr, 0, tiles, op, stream, variant, true);
+}
+
+int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int n_tensors,
+                    void *stream, int variant) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (n_tensors < 0 || (n_tensors > 0 && (!host_ptrs || !numel))) return fail(GA_EINVAL, "bad tensor list");
+    uint64_t total = 0;
+    int rc = build_layout(numel, n_tensors, &total);
+    if (rc) return rc;
+    if (total * kTileBytes > c->capacity_bytes)
+        return fail(GA_ECAPACITY, "gradient set needs %llu bucket bytes, capacity is %zu",
+                    (unsigned long long)(total * kTileBytes), c->capacity_bytes);
+    if (total == 0) return GA_OK;
+    if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
+    CUDA_TRY(cudaSetDevice(c->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    rc = drain_if_needed(c, stream);
+    if (rc) return rc;
+    for (int l = 0; l < c->n_local; ++l) {
+        size_t off = 0;
+        char *send = (char *)c->send_all[c->rank_base + l];
+        for (int i = 0; i < n_tensors; ++i) {
+            if (numel[i] > 0)
+                CUDA_TRY(cudaMemcpyAsync(send + off, host_ptrs[(size_t)l * n_tensors + i], (size_t)numel[i] * 4, cudaMemcpyHostToDevice, st));
+            off += tiles_for_elems(numel[i]) * kTileBytes;
+        }
+    }
+    rc = launch(c, nullptr, 0, (uint32_t)total, GA_OP_F32_AVG, stream, variant, true);
+    if (rc) return rc;
+    for (int l = 0; l < c->n_local; ++l) {
+        size_t off = 0;
+        const char *recv = (const char *)c->recv[l];
+        for (int i = 0; i < n_tensors; ++i) {
+            if (numel[i] > 0)
+                CUDA_TRY(cudaMemcpyAsync(host_ptrs[(size_t)l * n_tensors + i], recv + off, (size_t)numel[i] * 4, cudaMemcpyDeviceToHost, st));
+            off += tiles_for_elems(numel[i]) * kTileBytes;
+        }
+    }
+    return GA_OK;
+}
+
+int ga_bucket_acquire(ga_ctx *c, void *stream) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
+    return drain_if_needed(c, stream);
+}
+
+void *ga_send_ptr(ga_ctx *c, int local_rank) {
+    if (!c || local_rank < 0 || local_rank >= c->n_local) return nullptr;
+    return c->send_all[c->rank_base + local_rank];
+}
+
+void *ga_recv_ptr(ga_ctx *c, int local_rank) {
+    if (!c || local_rank < 0 || local_rank >= c->n_local) return nullptr;
+    return c->recv[local_rank];
+}
+
+int64_t ga_bucket_offset(const int64_t *numel, int n_tensors, int i) {
+    if (!numel || i < 0 || i > n_tensors) return -1;
+    int64_t off = 0;
+    for (int k = 0; k < i; ++k) off += (int64_t)tiles_for_elems(numel[k]) * kTileBytes;
+    return off;
+}
+
+int ga_world(const ga_ctx *c) { return c ? c->world : 0; }
+int ga_rank(const ga_ctx *c) { return c ? c->rank_base : -1; }
+int ga_n_local(const ga_ctx *c) { return c ? c->n_local : 0; }
+size_t ga_capacity(const ga_ctx *c) { return c ? c->capacity_bytes : 0; }
+
+int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
+    if (!c) return GA_VARIANT_ONESHOT;
+    return (c->world <= 2 || nbytes <= c->oneshot_max_bytes) ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
+}
+
+uint64_t ga_launch_count(const ga_ctx *c) { return c ? c->launches : 0; }
+
+int ga_last_grid(const ga_ctx *c, int *blocks, int *threads) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (blocks) *blocks = c->last_blocks;
+    if (threads) *threads = c->last_threads;
+    return GA_OK;
+}
+
+int ga_set_option(ga_ctx *c, int option, int64_t value) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    switch (option) {
+        case GA_OPT_ONESHOT_MAX_BYTES: c->oneshot_max_bytes = value < 0 ? 0 : (size_t)value; return GA_OK;
+        case GA_OPT_TIMEOUT_MS: c->timeout_ns = value <= 0 ? 0 : (unsigned long long)value * 1000000ull; return GA_OK;
+        case GA_OPT_MAX_BLOCKS: c->max_blocks_opt = value < 0 ? 0 : (int)value; return GA_OK;
+    }
+    return fail(GA_EINVAL, "unknown option %d", option);
+}
+
+int ga_status(ga_ctx *c) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    int s = *(volatile int *)c->status_host;
+    if (s != 0) {
+        c->broken = true;
+        return fail(s, "a kernel timed out waiting for a peer rank's flag; the context is unusable");
+    }
+    return GA_OK;
+}
+
+int ga_destroy(ga_ctx *c) {
+    if (!c) return GA_OK;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (int r = 0; r < c->world; ++r)
+        if (c->peer_base[r]) cudaIpcCloseMemHandle(c->peer_base[r]);
+    for (int l = 0; l < c->n_local; ++l) {
+        if (c->base[l]) cudaFree(c->base[l]);
+        if (c->recv[l]) cudaFree(c->recv[l]);
+    }
+    for (int i = 0; i < kSegRing; ++i) {
+        if (c->seg_host[i]) cudaFreeHost(c->seg_host[i]);
+        if (c->seg_dev[i]) cudaFree(c->seg_dev[i]);
+        if (c->seg_event[i]) cudaEventDestroy(c->seg_event[i]);
+    }
+    if (c->status_host) cudaFreeHost(c->status_host);
+    if (c->own_pads_dev) cudaFree(c->own_pads_dev);
+    free(c);
+    return GA_OK;
+}
+
+}  // extern "C"
