@@ -1,0 +1,404 @@
+#!/usr/bin/env python
+"""bench.py -- gradient-averaging throughput on B200 (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]                     # our arm
+    python bench.py --impl reference [--gpus N] [--steps K] [--warmup W]    # reference CPU arm
+    torchrun --nproc-per-node N ... bench.py --gpus N ...                   # N > 1, one rank per GPU
+
+A step is ONE pass of the hot path (`Trainer.average_gradients`, /root/reference/mnist/main.py:122-127)
+over one synthetic gradient set: every rank's S-byte fp32 gradient is replaced by the rank-order sum
+over all `world` ranks divided by float(world).
+
+  N = 1   world = 4 ranks hosted on the one B200 (BASELINE.json configs[1]: "gloo world_size=4 on host
+          cores vs 1 B200"), S = 64 MiB flat fp32 gradient per rank (the bucket size north_star quotes).
+          Everything moves through HBM, so the roofline bound is "hbm".
+  N > 1   world = N, one rank per GPU over CUDA-IPC/NVLink, same S.  The bound is NVLink; NCCL
+          all_reduce + div_ on a same-size buffer is timed in the same run.
+
+value   = world * busBW, busBW = (S / t) * 2(world-1)/world  (nccl-tests convention),
+          t = device time per step (CUDA events on the launching stream, max over ranks), inputs
+          resident in HBM.  Between steps the gradient buffers rotate over sets larger than L2.
+e2e     = same formula through the host-buffer entry point (ga_average_host): pinned host gradients,
+          H2D + kernel + D2H inside the timed region.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "grad-avg bus GB/s"
+UNIT = "GB/s"
+DEFAULT_BYTES = 64 << 20
+L2_BYTES = 126 << 20
+
+
+def bus_factor(world):
+    return 2.0 * (world - 1) / world if world > 1 else 0.0
+
+
+def agg_bus_gbps(world, nbytes, seconds):
+    """world * busBW in GB/s."""
+    return world * (nbytes / seconds) * bus_factor(world) / 1e9
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,utilization.gpu,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0, period_ms=50):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
+                 "-lms", str(period_ms)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, windows):
+        """windows: list of (t0, t1) wall-clock intervals that count as 'under load'."""
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        time.sleep(0.12)
+        self.proc.terminate()
+        sm, smax, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if not any(a <= t <= b + 0.06 for a, b in windows):
+                continue
+            f = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(f[0]))
+                smax = float(f[1])
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": smax,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu baseline (oracle.gloo_path on host cores) -- the only place oracle/ is executed
+# ------------------------------------------------------------------------------------------------
+def cpu_reference(world, nbytes, steps, warmup, budget_s):
+    """The reference's own averaging loop on gloo, `world` CPU processes, one flat fp32 buffer.
+    Each step covers a bounded sample of the workload so that the run fits `budget_s`."""
+    from oracle import gloo_path
+    est_s_per_byte = 1.2e-9 * max(1.0, world / 4.0)              # 64 MiB, ws=4 -> 72 ms
+    sample = int(min(nbytes, max(1 << 20, budget_s / max(1, steps + warmup) / est_s_per_byte)))
+    sample -= sample % 4
+    cores = os.cpu_count() or 1
+    threads = max(1, cores // world)
+    times = gloo_path.time_flat_average(world, sample // 4, steps, warmup=warmup, threads=threads)
+    sec = sum(times) / len(times)
+    return {
+        "value": agg_bus_gbps(world, sample, sec), "unit": UNIT, "cores": min(cores, world * threads),
+        "kind": "port", "ms_per_step": sec * 1e3, "world_size": world,
+        "sample": "%d of %d bytes per rank per step, %d steps, gloo tcp://127.0.0.1, %d procs x %d threads "
+                  "(host has %d cores%s); oracle/gloo_path.py = mnist/main.py:122-127 restated"
+                  % (sample, nbytes, steps, world, threads, cores, ", oversubscribed" if world > cores else ""),
+    }
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return                                                   # rank 0 alone runs the CPU arm
+    world = args.world or (4 if args.gpus == 1 else args.gpus)
+    t0 = time.time()
+    cb = cpu_reference(world, args.bytes, args.steps, args.warmup, budget_s=90.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(world, args.gpus, args.bytes, "gloo ring (torch)", None),
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.time() - t0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(world, gpus, nbytes, variant, rotate):
+    return {
+        "workload": "gradient averaging of one %d-byte fp32 gradient per rank, world_size=%d (%s); "
+                    "BASELINE configs[1] world size on 1 GPU, configs[3] 64 MiB bucket point"
+                    % (nbytes, world, "%d ranks hosted per GPU" % (world // gpus) if gpus == 1 else "one rank per GPU"),
+        "bytes_per_rank": nbytes, "world_size": world, "ranks_per_gpu": world // gpus if gpus == 1 else 1,
+        "variant": variant, "value_formula": "world * (S/t) * 2(world-1)/world",
+        "l2": None if rotate is None else "gradient buffers rotate over %d sets (%d MiB > L2) between steps"
+              % (rotate[0], rotate[1] >> 20),
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def algorithmic_hbm_bytes(world, nbytes, variant_name, hosted):
+    """Bytes the fused kernel's algorithm loads + stores per launch on ONE GPU hosting `hosted`
+    ranks (kernel table): pack 2S; one-shot: read W*S, write S; two-shot: reduce-scatter
+    read S + write 2S/W, all-gather read + write (W-1)S/W each."""
+    s, w = float(nbytes), world
+    per_rank = (w + 3) * s if variant_name == "oneshot" else 5.0 * s
+    return per_rank * hosted
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=400)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--bytes", type=int, default=DEFAULT_BYTES, help="gradient bytes per rank")
+    ap.add_argument("--world", type=int, default=0, help="world size when --gpus 1 (default 4)")
+    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the sweep / MNIST / cpu_baseline legs")
+    ap.add_argument("--profile", action="store_true", help="bare loop for ncu: no extras, no cpu leg, no e2e")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+
+    import torch
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import _lib
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
+    multi = args.gpus > 1
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if multi:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        world, hosted = dist.get_world_size(), 1
+        assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
+        avg = ga.GradAverager(capacity_bytes=args.bytes)
+    else:
+        torch.cuda.set_device(0)
+        world = args.world or 4
+        hosted = world
+        avg = ga.GradAverager(local_world=world, device=0, capacity_bytes=args.bytes)
+        dist = None
+    dev = torch.device("cuda", torch.cuda.current_device())
+    S = args.bytes - args.bytes % 4
+    n = S // 4
+    variant_id = {"auto": avg.pick_variant(S), "oneshot": ga.ONESHOT, "twoshot": ga.TWOSHOT}[args.variant]
+    variant_name = "oneshot" if variant_id == ga.ONESHOT else "twoshot"
+
+    # gradient sets: rotate so that consecutive steps never find their inputs in L2
+    n_sets = max(2, min(64, -(-(300 << 20) // (hosted * S))))
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    sets = [[torch.randn(n, device=dev, generator=gen) for _ in range(hosted)] for _ in range(n_sets)]
+
+    def step(i):
+        avg.all_reduce_([[g] for g in sets[i % n_sets]], average=True, variant=variant_id)
+
+    def barrier():
+        if multi:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if not multi:
+            return x
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    sampler = ClockSampler(index=torch.cuda.current_device()) if rank == 0 else None
+    windows = []
+
+    # ---- value: device-resident, K steps between two events, plus one event pair per launch ------
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    launches0 = avg.launch_count
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    w0 = time.time()
+    ev[0].record()
+    for i in range(args.steps):
+        step(i)
+        ev[i + 1].record()
+    torch.cuda.synchronize()
+    if multi:
+        dist.barrier()
+    windows.append((w0, time.time()))
+    gpu_launches = avg.launch_count - launches0
+    avg.check_status()
+    total_ms = max_over_ranks(ev[0].elapsed_time(ev[-1]))
+    per_launch_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    kernel_ms = max_over_ranks(sum(per_launch_ms) / len(per_launch_ms))
+    ms_per_step = total_ms / args.steps
+    value = agg_bus_gbps(world, S, ms_per_step / 1e3)
+    grid = avg.last_grid
+
+    # ---- roofline of the one kernel -------------------------------------------------------------
+    hbm_peak, peak_src = load_peaks()
+    alg_bytes = algorithmic_hbm_bytes(world, S, variant_name, hosted)
+    if multi:
+        bus = (S / (kernel_ms / 1e3)) * bus_factor(world) / 1e9
+        roofline = {"bound": "nvlink", "achieved": bus, "peak": 900.0, "unit": "GB/s", "frac": bus / 900.0,
+                    "traffic": None, "kernel": "ga_fused_kernel<%d,%s,f32avg>" % (world, variant_name),
+                    "kernel_ms": kernel_ms, "peak_source": "nominal NVLink 5 per direction per GPU (north_star); "
+                    "measured peer copy on this pool is 770 GB/s (B200_PROFILING.md)",
+                    "algorithmic": "busBW = S/t * 2(N-1)/N per GPU",
+                    "hbm_side": {"bytes": alg_bytes, "gbps": alg_bytes / (kernel_ms / 1e3) / 1e9, "peak": hbm_peak}}
+    else:
+        ach = alg_bytes / (kernel_ms / 1e3) / 1e9
+        roofline = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                    "traffic": load_traffic(), "kernel": "ga_fused_kernel<%d,%s,f32avg>" % (world, variant_name),
+                    "kernel_ms": kernel_ms, "peak_source": peak_src,
+                    "algorithmic": "%d hosted ranks x %s x S bytes per launch (DESIGN.md kernel table)"
+                                   % (hosted, "(W+3)" if variant_name == "oneshot" else "5")}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(world, args.gpus, S, variant_name, (n_sets, n_sets * hosted * S)),
+        "bus_gbps_per_rank": value / world, "alg_gbps_per_rank": S / (ms_per_step / 1e3) / 1e9,
+        "roofline": roofline, "gpu_launches": gpu_launches, "grid": {"blocks_per_rank": grid[0], "threads": grid[1]},
+    }
+
+    if not args.profile:
+        # ---- e2e: host buffers through ga_average_host ------------------------------------------
+        host_sets = [[torch.empty(n, dtype=torch.float32).pin_memory() for _ in range(hosted)] for _ in range(2)]
+        for hs in host_sets:
+            for t in hs:
+                t.normal_()
+        e2e_steps = max(3, min(args.steps, 20))
+        for i in range(3):
+            avg.average_host(host_sets[i % 2], variant=variant_id)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
+        e0.record()
+        for i in range(e2e_steps):
+            avg.average_host(host_sets[i % 2], variant=variant_id)
+        e1.record()
+        torch.cuda.synchronize()
+        if multi:
+            dist.barrier()
+        windows.append((w0, time.time()))
+        e2e_ms = max_over_ranks(e0.elapsed_time(e1)) / e2e_steps
+        line["e2e"] = {"value": agg_bus_gbps(world, S, e2e_ms / 1e3), "unit": UNIT, "ms_per_step": e2e_ms,
+                       "steps": e2e_steps, "h2d_bytes_per_step": hosted * S, "d2h_bytes_per_step": hosted * S,
+                       "api": "GradAverager.average_host -> ga_average_host (pinned host fp32 tensors)"}
+
+        # ---- NCCL on a same-size buffer, same run (N > 1) ---------------------------------------
+        if multi:
+            buf = torch.randn(n, device=dev, generator=gen)
+            for _ in range(5):
+                dist.all_reduce(buf)
+                buf.div_(float(world))
+            barrier()
+            k = max(10, min(args.steps, 100))
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(k):
+                dist.all_reduce(buf)               # mnist/main.py:126 on NCCL
+                buf.div_(float(world))             # mnist/main.py:127
+            e1.record()
+            torch.cuda.synchronize()
+            nccl_ms = max_over_ranks(e0.elapsed_time(e1)) / k
+            line["nccl_same_buffer"] = {"ms_per_step": nccl_ms, "bus_gbps_per_rank": S / (nccl_ms / 1e3) * bus_factor(world) / 1e9,
+                                        "what": "torch.distributed.all_reduce(SUM) + div_ on one %d-byte buffer" % S}
+
+        if not args.no_extras and rank == 0 and not multi:
+            line["extras"] = extras_single_gpu(avg, world, dev)
+
+    if sampler is not None:
+        line["clocks"] = sampler.stop(windows)
+
+    if not args.profile and not args.no_extras and rank == 0:
+        # CPU leg last, GPU idle: the reference's averaging on host cores, bounded sample
+        line["cpu_baseline"] = cpu_reference(world, S, steps=12, warmup=2, budget_s=20.0)
+
+    if multi:
+        dist.barrier()
+    avg.close()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if multi:
+        dist.destroy_process_group()
+
+
+def load_traffic():
+    """dram bytes per launch of the fused kernel from the committed ncu capture, if present."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get("dram_bytes_per_launch")
+        except Exception:
+            return None
+    return None
+
+
+def extras_single_gpu(avg, world, dev):
+    """Secondary numbers on the same GPU: the two real gradient sets and a size sweep, both
+    variants.  Device-timed, rotating buffers, 3 warm-ups each."""
+    import torch
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import workloads as shapes_only
+    out = {}
+
+    def time_set(shapes, variant, iters):
+        numel = sum(shapes_only.numel(s) for s in shapes)
+        nsets = max(2, min(48, -(-(300 << 20) // (world * numel * 4))))
+        sets = [[[torch.randn(s, device=dev) for s in shapes] for _ in range(world)] for _ in range(nsets)]
+        for i in range(3):
+            avg.all_reduce_(sets[i % nsets], average=True, variant=variant)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(iters):
+            avg.all_reduce_(sets[i % nsets], average=True, variant=variant)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        del sets
+        return {"us": ms * 1e3, "bus_gbps_per_rank": numel * 4 / (ms / 1e3) * bus_factor(world) / 1e9}
+
+    for name, shapes in (("mnist_cnn_1.72MB_8_tensors", shapes_only.MNIST_CNN_SHAPES),
+                         ("resnet18_46.76MB_62_tensors", shapes_only.resnet18_shapes())):
+        out[name] = {"oneshot": time_set(shapes, ga.ONESHOT, 200), "twoshot": time_set(shapes, ga.TWOSHOT, 200)}
+    sweep = {}
+    for kb in (4, 64, 1024, 16384):
+        shp = [(kb * 256,)]
+        sweep["%dKB" % kb] = {"oneshot": time_set(shp, ga.ONESHOT, 200), "twoshot": time_set(shp, ga.TWOSHOT, 200)}
+    out["sweep_world%d_hosted" % world] = sweep
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,94 @@
+"""CPU: the C-ABI library loads, exports every symbol include/gradavg.h declares, and fails
+loudly (no fallback) without a GPU.  No compute calls here."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "gradavg.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ga_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_header_symbols_exported(built):
+    from pytorch_distributed_example_b200 import _lib
+    names = _declared()
+    assert "ga_average" in names and "ga_create" in names and len(names) >= 20
+    for n in names:
+        assert hasattr(built, n), "library does not export %s" % n
+        assert n in _lib.SIGNATURES, "ctypes table lacks %s" % n
+    assert sorted(_lib.SIGNATURES) == names
+    # no torch / C++ types in the boundary: every exported ga_ symbol is unmangled
+    out = subprocess.check_output(["nm", "-D", "--defined-only", _lib.lib_path()]).decode()
+    exported = {l.split()[-1] for l in out.splitlines() if " T " in l}
+    assert set(names) <= exported
+    assert not [e for e in exported if e.startswith("_Z") and "ga_" in e and "kernel" not in e]
+
+
+def test_header_compiles_as_c(tmp_path):
+    src = tmp_path / "t.c"
+    src.write_text('#include "gradavg.h"\nint main(void){ga_ctx* c=0; return ga_world(c) + GA_VARIANT_TWOSHOT - 2;}\n')
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           "-c", str(src), "-o", str(tmp_path / "t.o")])
+
+
+def test_sm100a_only(built):
+    from pytorch_distributed_example_b200 import _lib
+    out = subprocess.check_output(["cuobjdump", "-lelf", _lib.lib_path()]).decode()
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_pure_host_entry_points(built):
+    numel = (ctypes.c_int64 * 4)(1, 512, 513, 0)
+    assert built.ga_bucket_offset(numel, 4, 0) == 0
+    assert built.ga_bucket_offset(numel, 4, 1) == 2048
+    assert built.ga_bucket_offset(numel, 4, 2) == 4096
+    assert built.ga_bucket_offset(numel, 4, 3) == 8192
+    assert built.ga_bucket_offset(numel, 4, 4) == 8192
+    assert built.ga_bucket_offset(numel, 4, 5) == -1
+    assert built.ga_world(None) == 0 and built.ga_rank(None) == -1
+    assert built.ga_average(None, None, None, 0, None, 0) == -1
+    assert b"NULL" in built.ga_last_error()
+    assert built.ga_destroy(None) == 0
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_fails_loudly_without_gpu(built):
+    import pytorch_distributed_example_b200 as ga
+    ctx = ctypes.c_void_p()
+    rc = built.ga_create_local(2, 0, 1 << 20, ctypes.byref(ctx))
+    assert rc == -2 and b"cuda" in built.ga_last_error().lower()
+    with pytest.raises(ga.GradAvgError):
+        ga.GradAverager(local_world=2, capacity_bytes=1 << 20)
+    avg = ga.GradAverager(local_world=2)
+    p = torch.nn.Parameter(torch.zeros(4))
+    p.grad = torch.ones(4)
+    with pytest.raises(ga.GradAvgError):            # CPU gradients are rejected, never averaged on the host
+        avg.average_gradients_local([[p], [p]])
+
+
+def test_missing_library_is_an_error(monkeypatch):
+    from pytorch_distributed_example_b200 import _lib
+    monkeypatch.setattr(_lib, "_LIB", None)
+    monkeypatch.setattr(_lib, "lib_path", lambda: "/nonexistent/libgradavg.so")
+    with pytest.raises(_lib.GradAvgError) as e:
+        _lib.load_library()
+    assert "no CPU or PyTorch fallback" in str(e.value)
+
+
+def test_product_never_touches_the_oracle():
+    pkg = os.path.join(ROOT, "pytorch-distributed-example_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".h", ".cuh")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+                assert "liboracle" not in text, f

@@ -216,7 +216,7 @@ def test_int32_sum_toy(lib, golden_dir):
     toy = json.load(open(os.path.join(golden_dir, "toy.json")))["worlds"]
     for ws_s, outs in toy.items():
         world = int(ws_s)
-        rows = [re.findall(r"value: (\d+), reduced sum: ([\d.]+)", o) for o in outs]
+        rows = [re.findall(r"value: (\d+), reduced sum: (\d+\.\d+)", o) for o in outs]
         w = LocalWorld(lib, world, 1 << 20)
         try:
             for step in range(len(rows[0])):

@@ -1,0 +1,106 @@
+"""CPU: host-side logic of the shim -- layout arithmetic, the `distributed` stand-in, the Trainer
+patch -- including a world_size-2 gloo run of the multi-process code path up to the point where
+a GPU would be needed."""
+import os
+import sys
+
+import pytest
+import torch
+
+import pytorch_distributed_example_b200 as ga
+from pytorch_distributed_example_b200 import averager, distributed
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_bucket_layout_arithmetic():
+    assert averager.bucket_bytes([1]) == 2048
+    assert averager.bucket_bytes([512, 513, 0]) == 2048 + 4096
+    import oracle
+    mn = averager.bucket_bytes(oracle.numel_of(oracle.MNIST_CNN_SHAPES))
+    assert mn % 2048 == 0 and 1724320 <= mn <= 1724320 + 8 * 2048
+
+
+def test_reduce_op_alias_and_passthrough():
+    assert distributed.reduce_op.SUM == torch.distributed.ReduceOp.SUM
+    assert distributed.ReduceOp is torch.distributed.ReduceOp
+    assert distributed.is_available is torch.distributed.is_available       # everything else: torch's
+
+
+def test_install_patches_class_and_instance():
+    class Trainer:                       # same surface as mnist/main.py:54-63,122
+        def __init__(self, net):
+            self.net = net
+
+        def average_gradients(self):
+            raise AssertionError("reference path must not run")
+
+    calls = []
+    orig = ga.trainer.average_gradients
+    ga.trainer.average_gradients = lambda params, variant=None: calls.append((list(params), variant))
+    try:
+        net = torch.nn.Linear(3, 2)
+        ga.install(Trainer, variant="twoshot")
+        Trainer(net).average_gradients()
+        assert len(calls) == 1 and len(calls[0][0]) == 2 and calls[0][1] == "twoshot"
+        t = Trainer(net)
+        ga.install(t)
+        t.average_gradients()
+        assert len(calls) == 2
+    finally:
+        ga.trainer.average_gradients = orig
+
+
+def test_missing_grad_raises_like_reference():
+    net = torch.nn.Linear(2, 2)          # no backward yet: p.grad is None -> `.data` AttributeError in the reference
+    with pytest.raises(AttributeError):
+        ga.GradAverager._grads_of(net.parameters())
+
+
+def _w2(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    from pytorch_distributed_example_b200 import distributed as dist
+    import pytorch_distributed_example_b200 as ga2
+    dist.init_process_group(backend="gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    out = {"ws": dist.get_world_size(), "rank": dist.get_rank()}
+    tok = dist.new_group(ranks=list(range(world)))           # toy/main.py:15-16 -> token, no new torch group
+    out["token"] = type(tok).__name__
+    avg = ga2.GradAverager()                                  # binds to the default group, no GPU needed yet
+    out["avg_ws"], out["avg_rank"] = avg.world_size, avg.rank
+    try:
+        dist.all_reduce(torch.IntTensor([rank + 1]), op=dist.reduce_op.SUM, group=tok)
+        out["err"] = None
+    except ga2.GradAvgError as e:                             # no GPU here: must fail, not fall back to gloo
+        out["err"] = str(e)
+    try:
+        dist.all_reduce(torch.zeros(2, dtype=torch.float64))
+    except ga2.GradAvgError as e:
+        out["dtype_err"] = str(e)
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put(out)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour of the multi-process path")
+def test_world2_gloo_host_path():
+    import torch.multiprocessing as mp
+    from oracle.gloo_path import free_port
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = free_port()
+    procs = [ctx.Process(target=_w2, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    res = sorted([q.get(timeout=120) for _ in procs], key=lambda d: d["rank"])
+    [p.join(60) for p in procs]
+    for r, d in enumerate(res):
+        assert d["ws"] == 2 and d["rank"] == r and d["avg_ws"] == 2 and d["avg_rank"] == r
+        assert d["token"] == "WorldToken"
+        assert d["err"] is not None and "no CPU fallback" in d["err"]
+        assert "float64" in d["dtype_err"]
+
+
+def test_workload_shapes_agree_with_oracle_tables():
+    import oracle
+    from pytorch_distributed_example_b200 import workloads
+    assert workloads.MNIST_CNN_SHAPES == oracle.MNIST_CNN_SHAPES
+    assert workloads.resnet18_shapes() == oracle.resnet18_shapes()

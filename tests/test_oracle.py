@@ -1,0 +1,107 @@
+"""CPU: the oracle against the golden files made from the REAL reference (tests/golden/make_golden.py).
+
+The reference has no tests, vectors or known answers of its own for this path;
+the pin is therefore its own output, recorded here: `Trainer.average_gradients` on gloo for
+ws in {2,3,4,8} and toy `foo`'s printed sums.
+"""
+import hashlib
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import gloo_path
+
+
+def _mini(golden_dir, world):
+    z = np.load(os.path.join(golden_dir, "mini_ws%d.npz" % world))
+    n = len(oracle.MINI_SHAPES)
+    ins = [[z["in_r%d_t%d" % (r, i)] for i in range(n)] for r in range(world)]
+    out = [z["out_t%d" % i] for i in range(n)]
+    return ins, out
+
+
+def test_seeded_inputs_match_golden(golden_dir):
+    """The generator used on the GPU side reproduces the inputs the reference run consumed."""
+    for world in (2, 8):
+        ins, _ = _mini(golden_dir, world)
+        for r in range(world):
+            mine = oracle.seeded_grads(oracle.MINI_SHAPES, r)
+            for a, b in zip(ins[r], mine):
+                assert a.tobytes() == b.numpy().tobytes()
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+def test_fold_vs_reference_output(golden_dir, world):
+    """Rank-order fold (numpy and C) against the reference's gloo result: bit-exact at ws=2,
+    backward error <= 1e-6 at ws>=3 where gloo's ring adds in another order."""
+    ins, out = _mini(golden_dir, world)
+    for i in range(len(out)):
+        per_rank = [ins[r][i] for r in range(world)]
+        f_np = oracle.fold_average(per_rank)
+        f_c = oracle.fold_average_c(per_rank)
+        assert f_np.tobytes() == f_c.tobytes()
+        if world == 2:
+            assert f_np.tobytes() == out[i].tobytes()
+        else:
+            assert oracle.backward_error(f_np, out[i], per_rank) <= 1e-6
+
+
+@pytest.mark.parametrize("world", [2, 3, 4, 8])
+def test_fold_sha_on_full_mnist_set(golden_dir, world):
+    meta = json.load(open(os.path.join(golden_dir, "mnist_cnn.json")))["worlds"][str(world)]
+    for name, gen in (("signed", oracle.seeded_grads), ("positive", oracle.seeded_positive_grads)):
+        ins = [np.concatenate([g.numpy().ravel() for g in gen(oracle.MNIST_CNN_SHAPES, r)]) for r in range(world)]
+        fold = oracle.fold_average_c(ins)
+        assert hashlib.sha256(fold.tobytes()).hexdigest() == meta[name]["fold_sha256"]
+        if world == 2:
+            assert meta[name]["sha256"] == meta[name]["fold_sha256"]
+        assert meta[name]["backward_err_vs_fold"] <= 1e-6
+    # raw relative error <= 1e-6 holds on the non-cancelling set, not on signed data (F3)
+    assert meta["positive"]["raw_rel_vs_fold"] <= 1e-6
+
+
+def test_division_is_not_reciprocal_multiply():
+    """x / 3.0f differs from x * (1/3.0f); the fold must divide."""
+    x = np.array([1.0, 5.0, 7.0, 1e-3, 123456.7], dtype=np.float32)
+    one = [x, np.zeros_like(x), np.zeros_like(x)]
+    got = oracle.fold_average_c(one)
+    assert got.tobytes() == (x / np.float32(3.0)).tobytes()
+    assert got.tobytes() != (x * (np.float32(1.0) / np.float32(3.0))).astype(np.float32).tobytes()
+
+
+def test_gloo_port_reproduces_reference(golden_dir):
+    """oracle.gloo_path (the restated loop, what bench.py times as the CPU baseline) run live on
+    gloo gives the reference's bytes: full arrays at ws=3 (mini set), sha256 at ws=2 (full set)."""
+    _, out = _mini(golden_dir, 3)
+    got = gloo_path.gloo_average(3, oracle.MINI_SHAPES)
+    for a, b in zip(got, out):
+        assert a.tobytes() == b.tobytes()
+    meta = json.load(open(os.path.join(golden_dir, "mnist_cnn.json")))["worlds"]["2"]["signed"]
+    got = gloo_path.gloo_average(2, oracle.MNIST_CNN_SHAPES)
+    flat = np.concatenate([a.ravel() for a in got])
+    assert hashlib.sha256(flat.tobytes()).hexdigest() == meta["sha256"]
+
+
+def test_toy_golden_and_int_fold(golden_dir):
+    toy = json.load(open(os.path.join(golden_dir, "toy.json")))["worlds"]
+    for ws, outs in toy.items():
+        rows = [re.findall(r"value: (\d+), reduced sum: (\d+\.\d+)", o) for o in outs]
+        assert len(rows) == int(ws)
+        for step in range(3):
+            vals = [np.array([int(rows[r][step][0])], dtype=np.int32) for r in range(int(ws))]
+            s = oracle.fold_sum_i32(vals)
+            assert s.tobytes() == oracle.fold_sum_i32_c(vals).tobytes()
+            for r in range(int(ws)):
+                assert float(s[0]) == float(rows[r][step][1])
+    big = [np.array([2**31 - 1, -5], dtype=np.int32), np.array([1, -2**31], dtype=np.int32)]
+    assert oracle.fold_sum_i32_c(big).tolist() == [-2**31, 2**31 - 5]
+
+
+def test_shape_tables():
+    assert sum(oracle.numel_of(oracle.MNIST_CNN_SHAPES)) == 431080
+    rs = oracle.resnet18_shapes()
+    assert len(rs) == 62 and sum(oracle.numel_of(rs)) == 11689512
