@@ -298,13 +298,13 @@ def main():
                 t.normal_()
         e2e_steps = max(3, min(args.steps, 20))
         for i in range(3):
-            avg.average_host(host_sets[i % 2], variant=variant_id)
+            avg.average_host([[t] for t in host_sets[i % 2]], variant=variant_id)
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         w0 = time.time()
         e0.record()
         for i in range(e2e_steps):
-            avg.average_host(host_sets[i % 2], variant=variant_id)
+            avg.average_host([[t] for t in host_sets[i % 2]], variant=variant_id)
         e1.record()
         torch.cuda.synchronize()
         if multi:

@@ -169,6 +169,9 @@ class GradAverager:
         return ptrs, numel, n
 
     def _run_tensors(self, per_rank_tensors, op, dtype, variant):
+        if len(per_rank_tensors) != self.n_local:
+            raise GradAvgError(_lib.GA_EINVAL, "got %d tensor lists for %d hosted rank(s)"
+                               % (len(per_rank_tensors), self.n_local))
         with self._lock:
             numels = [t.numel() for t in per_rank_tensors[0]]
             self._ensure(bucket_bytes(numels))
@@ -210,6 +213,9 @@ class GradAverager:
         stream-ordered; the caller synchronises the stream before reading the tensors."""
         if per_rank_host_tensors and torch.is_tensor(per_rank_host_tensors[0]):
             per_rank_host_tensors = [list(per_rank_host_tensors)]
+        if len(per_rank_host_tensors) != self.n_local:
+            raise GradAvgError(_lib.GA_EINVAL, "got %d tensor lists for %d hosted rank(s)"
+                               % (len(per_rank_host_tensors), self.n_local))
         with self._lock:
             numels = [t.numel() for t in per_rank_host_tensors[0]]
             self._ensure(bucket_bytes(numels))
@@ -217,6 +223,8 @@ class GradAverager:
             ptrs = (ctypes.c_void_p * (n * len(per_rank_host_tensors)))()
             k = 0
             for ts in per_rank_host_tensors:
+                if [t.numel() for t in ts] != numels:
+                    raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different tensor sizes")
                 for t in ts:
                     if t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
                         raise GradAvgError(_lib.GA_EINVAL, "average_host needs contiguous CPU fp32 tensors")

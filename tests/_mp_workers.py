@@ -1,0 +1,107 @@
+"""Worker bodies for the multi-process tests (spawn needs importable top-level functions)."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def ipc_world(rank, world, port, q, backend):
+    """One rank per GPU over real CUDA-IPC peer memory: parity vs the rank-order fold."""
+    import numpy as np
+    import torch
+    import oracle
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import distributed as dist, _lib
+
+    out = {"rank": rank, "fail": []}
+    try:
+        os.environ.setdefault("GA_TIMEOUT_MS", "8000")
+        dist.init_process_group(backend=backend, init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+        assert torch.cuda.current_device() == rank          # F5 fix applied by the shim
+        avg = ga.default_averager()
+
+        def fold(shapes, gen=oracle.seeded_grads, seed=1234):
+            host = [[g.numpy() for g in gen(shapes, r, seed)] for r in range(world)]
+            return host, [oracle.fold_average_c([host[r][i] for r in range(world)]) for i in range(len(shapes))]
+
+        class P:
+            def __init__(self, g):
+                self.grad = g
+
+        # 1. the reference call on the MNIST set and the mini set, both variants
+        for name, shapes in (("mini", oracle.MINI_SHAPES), ("mnist", oracle.MNIST_CNN_SHAPES)):
+            host, want = fold(shapes)
+            for variant in ("oneshot", "twoshot"):
+                params = [P(torch.from_numpy(a).cuda()) for a in host[rank]]
+                ga.average_gradients(params, variant=variant)
+                avg.check_status()
+                for i, (p, w) in enumerate(zip(params, want)):
+                    if p.grad.cpu().numpy().tobytes() != w.tobytes():
+                        out["fail"].append("%s %s tensor %d" % (name, variant, i))
+
+        # 2. skew stress: random extra GPU work before the call on a random rank, fresh pointers,
+        #    alternating sizes and variants, no host sync between steps
+        rng = np.random.default_rng(42)                       # same stream on every rank
+        sets = [oracle.MINI_SHAPES, [(70001,)], oracle.MNIST_CNN_SHAPES, [(5,)]]
+        keep = []
+        for step in range(200):
+            shapes = sets[step % len(sets)]
+            variant = "oneshot" if (step // 3) % 2 == 0 else "twoshot"
+            slow = int(rng.integers(0, world))
+            cycles = int(rng.integers(0, 3_000_000))
+            if rank == slow:
+                torch.cuda._sleep(cycles)
+            g = torch.Generator(device="cuda").manual_seed(10_000 * step + rank)
+            params = [P(torch.randn(s, device="cuda", generator=g)) for s in shapes]
+            ins = [p.grad.clone() for p in params] if step % 20 == 0 else None
+            ga.average_gradients(params, variant=variant)
+            if ins is not None:
+                keep.append((step, shapes, ins, params))
+        avg.check_status()
+        import torch.distributed as tdist
+        for step, shapes, ins, params in keep:
+            for i, (x, p) in enumerate(zip(ins, params)):
+                gathered = [torch.empty_like(x) for _ in range(world)]
+                if backend == "gloo":
+                    xs = x.cpu()
+                    gathered = [torch.empty_like(xs) for _ in range(world)]
+                    tdist.all_gather(gathered, xs)
+                else:
+                    tdist.all_gather(gathered, x)
+                want = oracle.fold_average_c([t.cpu().numpy() for t in gathered])
+                if p.grad.cpu().numpy().tobytes() != want.tobytes():
+                    out["fail"].append("skew step %d tensor %d" % (step, i))
+
+        # 3. toy path: int32 SUM of a host IntTensor through distributed.all_reduce (toy/main.py:15-20)
+        group = dist.new_group(ranks=list(range(world)))
+        t = torch.IntTensor([rank + 3])
+        dist.all_reduce(t, op=dist.reduce_op.SUM, group=group)
+        if int(t) != sum(r + 3 for r in range(world)):
+            out["fail"].append("toy int32 sum %d" % int(t))
+
+        # 4. bucket-direct and host forms
+        n = 262144 + 3
+        host = [np.random.default_rng(r).standard_normal(n).astype(np.float32) for r in range(world)]
+        want = oracle.fold_average_c(host)
+        avg.bucket_acquire()
+        for variant in ("oneshot", "twoshot"):
+            avg.send_view(n * 4).copy_(torch.from_numpy(host[rank]).cuda())
+            avg.allreduce_bucket(n * 4, variant=variant)
+            avg.check_status()
+            if avg.recv_view(n * 4).cpu().numpy().tobytes() != want.tobytes():
+                out["fail"].append("bucket-direct " + variant)
+            pinned = torch.from_numpy(host[rank].copy()).pin_memory()
+            avg.average_host([pinned], variant=variant)
+            torch.cuda.synchronize()
+            if pinned.numpy().tobytes() != want.tobytes():
+                out["fail"].append("host form " + variant)
+        out["launches"] = avg.launch_count
+        tdist.barrier()
+        ga.reset_default_averager()
+        tdist.destroy_process_group()
+    except Exception as e:                                    # report, never hang the parent
+        import traceback
+        out["fail"].append("exception: %s\n%s" % (e, traceback.format_exc()))
+    q.put(out)

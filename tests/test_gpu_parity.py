@@ -266,6 +266,7 @@ def test_capacity_and_argument_errors(lib):
         numel = (ctypes.c_int64 * 1)(100000)
         rc = lib.ga_average(w.ctx, ptrs, numel, 1, None, ONESHOT)
         assert rc == -3 and b"capacity" in lib.ga_last_error()
+        numel[0] = 100
         assert lib.ga_average(w.ctx, ptrs, numel, 1, None, 7) == -1
         numel[0] = -1
         assert lib.ga_average(w.ctx, ptrs, numel, 1, None, ONESHOT) == -1
