@@ -166,6 +166,38 @@ int ga_set_option(ga_ctx *ctx, int option, int64_t value);
  * then unusable).  Reads a host-mapped word; call after synchronising the stream. */
 int ga_status(ga_ctx *ctx);
 
+/*
+ * Gradient average for callers that must not allocate.  No counterpart in the reference.
+ *
+ * Who needs it: code that runs where a cudaMalloc is off limits -- inside a host application
+ * whose own pool has claimed the GPU's memory and treats foreign allocations as a bug, inside a
+ * latency-critical region that cannot afford the device-wide synchronisation cudaMalloc/cudaFree
+ * imply, or under a plug-in contract that forbids allocation after start-up.  Every other entry
+ * point needs a context, and ga_create / ga_create_local allocate (bucket, flag pad, pinned status
+ * word).  This one needs no context and calls no cudaMalloc, cudaFree, cudaHostAlloc or any
+ * library routine that allocates: bucket, flags and status live in a fixed array inside the
+ * library image.
+ *
+ * What it does: exactly ga_average on a ga_create_local(world) context -- all `world` ranks hosted
+ * on `device`, grad_ptrs = world * n_tensors device pointers (rank-major), fp32, averaged in place,
+ * rank-order sum then one division, one kernel on `stream` -- and its results are bit-identical
+ * to that call.
+ *
+ * Limits: world * (bucket bytes of the set, each tensor padded to 2 KiB) <= 8 MiB, and
+ * world * n_tensors <= 128 pointers; beyond either it returns GA_ECAPACITY and launches nothing.
+ * The 8.6 MB array is resident on every GPU that loads the library, until the process exits.
+ *
+ * First call on a device: resolves the array's address on that device (cudaGetSymbolAddress, with
+ * the device made current) and caches it.  Make that first call before starting any stream capture.
+ *
+ * All calls on one device share the one array.  It keeps whatever the previous call left, so each
+ * call first clears, on `stream`, the words its flag protocol counts up from zero.  Two calls whose
+ * GPU work can overlap (different streams without an event between them, or two host threads)
+ * race on that array and give wrong gradients; order them yourself.
+ */
+int ga_average_static(int world, int device, const void *const *grad_ptrs, const int64_t *numel,
+                      int n_tensors, void *stream, int variant);
+
 /* Frees everything.  Every rank must have finished its last call (barrier first). */
 int ga_destroy(ga_ctx *ctx);
 

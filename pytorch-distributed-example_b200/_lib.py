@@ -41,6 +41,8 @@ SIGNATURES = {
     "ga_last_grid": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_int)]),
     "ga_set_option": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int64]),
     "ga_status": (_c.c_int, [_c.c_void_p]),
+    "ga_average_static": (_c.c_int, [_c.c_int, _c.c_int, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
+                                     _c.c_void_p, _c.c_int]),
     "ga_destroy": (_c.c_int, [_c.c_void_p]),
 }
 

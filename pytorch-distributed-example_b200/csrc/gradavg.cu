@@ -870,3 +870,122 @@ int ga_destroy(ga_ctx *c) {
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// ga_average_static: the hosted-world average with NO allocation anywhere
+// ------------------------------------------------------------------------------------------
+// Some callers of this library are not allowed to allocate device memory at the moment they
+// need a gradient average: code that runs while another component owns the allocator (a
+// framework that has reserved "all" of HBM for its own pool and treats any foreign cudaMalloc as
+// an out-of-memory risk), code inside a latency-critical section where the implicit device
+// synchronisation of cudaMalloc/cudaFree is unacceptable, and plug-in hosts that forbid
+// allocation after start-up.  ga_create cannot serve them: it cudaMallocs the bucket, the flag
+// pad and a pinned status word.  This entry point keeps all of that in one file-scope device
+// array instead, which the driver places when the library is loaded and which every GPU that
+// loads the library keeps until the process exits.
+namespace {
+
+constexpr size_t kStaticBucketBytes = (size_t)8 << 20;    // bucket space shared by ALL hosted ranks
+constexpr size_t kStaticStatusBytes = 256;
+constexpr size_t kStaticPadsBytes = kMaxWorld * kPadBytes;
+constexpr size_t kStaticBytes = kStaticPadsBytes + kStaticStatusBytes + kStaticBucketBytes;
+constexpr int kStaticMaxDevices = 64;
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never an address to pass on.
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
+
+struct StaticDevice {
+    bool ready;
+    unsigned char *scratch;      // device address of g_static_scratch on this device
+    int sm_count;
+    int blocks_per_sm[2][kMaxWorld + 1];
+};
+StaticDevice g_static_dev[kStaticMaxDevices];
+
+}  // namespace
+
+extern "C" int ga_average_static(int world, int device, const void *const *grad_ptrs, const int64_t *numel,
+                                 int n_tensors, void *stream, int variant) {
+    if (world < 1 || world > kMaxWorld) return fail(GA_EINVAL, "world=%d outside 1..%d", world, kMaxWorld);
+    if (device < 0 || device >= kStaticMaxDevices) return fail(GA_EINVAL, "device=%d outside 0..%d", device, kStaticMaxDevices - 1);
+    if (n_tensors < 0 || (n_tensors > 0 && (!grad_ptrs || !numel))) return fail(GA_EINVAL, "bad tensor list");
+    if ((size_t)n_tensors * world > (size_t)kInlineSegs)
+        return fail(GA_ECAPACITY, "ga_average_static carries at most %d pointers (world * n_tensors = %zu): "
+                    "a larger table would need a device allocation", kInlineSegs, (size_t)n_tensors * world);
+    uint64_t total = 0;
+    int rc = build_layout(numel, n_tensors, &total);
+    if (rc) return rc;
+    if (total * kTileBytes * world > kStaticBucketBytes)
+        return fail(GA_ECAPACITY, "ga_average_static: %d ranks x %llu bucket bytes exceed the built-in %zu-byte scratch; "
+                    "use ga_create_local + ga_average for larger gradient sets",
+                    world, (unsigned long long)(total * kTileBytes), kStaticBucketBytes);
+    if (total == 0) return GA_OK;
+    if (variant == GA_VARIANT_AUTO)
+        variant = (world <= 2 || total * kTileBytes <= ((size_t)512 << 10)) ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
+    if (variant != GA_VARIANT_ONESHOT && variant != GA_VARIANT_TWOSHOT) return fail(GA_EINVAL, "unknown variant %d", variant);
+
+    CUDA_TRY(cudaSetDevice(device));
+    StaticDevice &sd = g_static_dev[device];
+    if (!sd.ready) {
+        // Once per device, with that device current: resolve the array's address ON THIS DEVICE.
+        void *addr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&addr, g_static_scratch));
+        if (!addr) return fail(GA_ECUDA, "cudaGetSymbolAddress returned a null address");
+        CUDA_TRY(cudaDeviceGetAttribute(&sd.sm_count, cudaDevAttrMultiProcessorCount, device));
+        sd.scratch = (unsigned char *)addr;
+        sd.ready = true;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    // The array still holds the previous call's flags: everything the protocol counts from zero
+    // (flag rows, done words, block counter, status) is cleared on the stream before each launch.
+    CUDA_TRY(cudaMemsetAsync(sd.scratch, 0, (size_t)world * kPadBytes, st));
+    CUDA_TRY(cudaMemsetAsync(sd.scratch + kStaticPadsBytes, 0, kStaticStatusBytes, st));
+
+    Params p;
+    memset(&p, 0, sizeof(p));
+    const size_t per_rank = (size_t)total * kTileBytes;
+    for (int r = 0; r < world; ++r) {
+        p.pad[r] = (Pad *)(sd.scratch + (size_t)r * kPadBytes);
+        p.send[r] = sd.scratch + kStaticPadsBytes + kStaticStatusBytes + (size_t)r * per_rank;
+    }
+    p.status = (int *)(sd.scratch + kStaticPadsBytes);
+    p.timeout_ns = 30ull * 1000000000ull;
+    p.n_seg = (uint32_t)n_tensors;
+    p.total_tiles = (uint32_t)total;
+    p.shard_tiles = ((uint32_t)total + world - 1) / world;
+    p.epoch = 1;
+    p.rank_base = 0;
+    p.direct = 0;
+    for (int l = 0; l < world; ++l) {
+        uint32_t start = 0;
+        for (int i = 0; i < n_tensors; ++i) {
+            Seg &s = p.inline_segs[(size_t)l * n_tensors + i];
+            s.ptr = grad_ptrs[(size_t)l * n_tensors + i];
+            s.start_tile = start;
+            s.numel = (uint32_t)numel[i];
+            if (numel[i] > 0 && !s.ptr) return fail(GA_EINVAL, "pointer %d of hosted rank %d is NULL", i, l);
+            if (((uintptr_t)s.ptr & 3) != 0) return fail(GA_EINVAL, "pointer %d of hosted rank %d is not 4-byte aligned", i, l);
+            start += (uint32_t)tiles_for_elems(numel[i]);
+        }
+    }
+
+    KernelFn fn = pick_kernel(world, variant, GA_OP_F32_AVG);
+    int &bps = sd.blocks_per_sm[variant == GA_VARIANT_TWOSHOT][world];
+    if (bps == 0) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)fn, kThreads, 0) != cudaSuccess || n < 1) n = 1;
+        bps = n;
+    }
+    const uint32_t slots = variant == GA_VARIANT_TWOSHOT ? p.shard_tiles : p.total_tiles;
+    const int wpb = kThreads / 32;
+    int resident = bps * sd.sm_count / world;
+    if (resident > kMaxBlocks) resident = kMaxBlocks;
+    if (resident < 1) resident = 1;
+    int blocks = (int)((slots + wpb - 1) / wpb);
+    if (blocks > resident) blocks = resident;
+    dim3 grid(blocks, world), block(kThreads);
+    void *args[] = {&p};
+    if (world > 1) CUDA_TRY(cudaLaunchCooperativeKernel((const void *)fn, grid, block, args, 0, st));
+    else CUDA_TRY(cudaLaunchKernel((const void *)fn, grid, block, args, 0, st));
+    return GA_OK;
+}
