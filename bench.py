@@ -180,6 +180,8 @@ def main():
     ap.add_argument("--world", type=int, default=0, help="world size when --gpus 1 (default 4)")
     ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot"])
     ap.add_argument("--no-extras", action="store_true", help="skip the sweep / MNIST / cpu_baseline legs")
+    ap.add_argument("--sweep", action="store_true", help="N > 1: size sweep 4 KB..1 GB, ours (both variants, fused and bucket) vs NCCL")
+    ap.add_argument("--sweep-max", type=int, default=1 << 30)
     ap.add_argument("--profile", action="store_true", help="bare loop for ncu: no extras, no cpu leg, no e2e")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -336,6 +338,8 @@ def main():
 
         if not args.no_extras and rank == 0 and not multi:
             line["extras"] = extras_single_gpu(avg, world, dev)
+        if multi and args.sweep:
+            line["sweep"] = sweep_multi(avg, world, dev, dist, args.sweep_max)
 
     if sampler is not None:
         line["clocks"] = sampler.stop(windows)
@@ -351,6 +355,72 @@ def main():
         print(json.dumps(line), flush=True)
     if multi:
         dist.destroy_process_group()
+
+
+def sweep_multi(avg, world, dev, dist, max_bytes):
+    """Config 4: flat fp32 buffer, 4 KB * 4^k up to 1 GB plus the two real set sizes; per size the
+    fused call (pack + reduce + unpack on a gradient tensor), the bucket-direct call (reduce only),
+    both variants, and NCCL all_reduce + div_ on the same-size buffer.  Median of per-iteration
+    max over ranks, device-timed."""
+    import torch
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import _lib
+    sizes = [4 << 10, 16 << 10, 64 << 10, 256 << 10, 1 << 20, 1724320, 4 << 20, 16 << 20, 46758048, 64 << 20,
+             256 << 20, 1 << 30]
+    sizes = [s for s in sizes if s <= max_bytes]
+    avg.reserve(max(sizes) + 4096)
+    out = []
+
+    def timed(fn, iters, warm=5):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+        evs[0].record()
+        for i in range(iters):
+            fn()
+            evs[i + 1].record()
+        torch.cuda.synchronize()
+        t = torch.tensor([evs[i].elapsed_time(evs[i + 1]) for i in range(iters)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = t.sort().values
+        return float(t[iters // 2]) * 1e3, float(t[0]) * 1e3          # median, best (us)
+
+    for S in sizes:
+        n = S // 4
+        iters = 50 if S < (256 << 20) else 10
+        # rotate two buffers so that no iteration finds its own input in L2 (>= 64 MiB: exceeds L2 anyway)
+        bufs = [torch.randn(n, device=dev) for _ in range(2 if S >= (32 << 20) else 8)]
+        k = [0]
+        row = {"bytes": S}
+        for vname, v in (("oneshot", ga.ONESHOT), ("twoshot", ga.TWOSHOT)):
+            if vname == "oneshot" and S > (64 << 20) and world > 2:
+                continue
+
+            def fused():
+                k[0] += 1
+                avg.all_reduce_([[bufs[k[0] % len(bufs)]]], average=True, variant=v)
+            med, best = timed(fused, iters)
+            row["fused_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+            avg.bucket_acquire()
+
+            def bucket():
+                avg.allreduce_bucket(S, variant=v)
+            med, best = timed(bucket, iters)
+            row["bucket_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+
+        def nccl():
+            k[0] += 1
+            b = bufs[k[0] % len(bufs)]
+            dist.all_reduce(b)
+            b.div_(float(world))
+        med, best = timed(nccl, iters)
+        row["nccl_allreduce_div"] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+        out.append(row)
+        del bufs
+        avg.check_status()
+    return out
 
 
 def load_traffic():
