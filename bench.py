@@ -40,6 +40,14 @@ DEFAULT_BYTES = 64 << 20
 L2_BYTES = 126 << 20
 
 
+_T0 = time.time()
+
+
+def stage(msg):
+    """Progress line on stderr (the JSON line on stdout stays alone)."""
+    print("[bench %6.1fs rank %s] %s" % (time.time() - _T0, os.environ.get("RANK", "0"), msg), file=sys.stderr, flush=True)
+
+
 def bus_factor(world):
     return 2.0 * (world - 1) / world if world > 1 else 0.0
 
@@ -241,9 +249,12 @@ def main():
     windows = []
 
     # ---- value: device-resident, K steps between two events, plus one event pair per launch ------
+    stage("context ready: world=%d hosted=%d S=%d variant=%s sets=%d" % (world, hosted, S, variant_name, n_sets))
     for i in range(args.warmup):
         step(i)
+    avg.check_status()                      # a peer that never arrives surfaces here, not as a hung bench
     barrier()
+    stage("warm-up done, grid=%s" % (avg.last_grid,))
     launches0 = avg.launch_count
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     w0 = time.time()
@@ -257,6 +268,7 @@ def main():
     windows.append((w0, time.time()))
     gpu_launches = avg.launch_count - launches0
     avg.check_status()
+    stage("timed region done")
     total_ms = max_over_ranks(ev[0].elapsed_time(ev[-1]))
     per_launch_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     kernel_ms = max_over_ranks(sum(per_launch_ms) / len(per_launch_ms))
@@ -312,6 +324,8 @@ def main():
         if multi:
             dist.barrier()
         windows.append((w0, time.time()))
+        avg.check_status()
+        stage("e2e done")
         e2e_ms = max_over_ranks(e0.elapsed_time(e1)) / e2e_steps
         line["e2e"] = {"value": agg_bus_gbps(world, S, e2e_ms / 1e3), "unit": UNIT, "ms_per_step": e2e_ms,
                        "steps": e2e_steps, "h2d_bytes_per_step": hosted * S, "d2h_bytes_per_step": hosted * S,
@@ -332,6 +346,7 @@ def main():
                 buf.div_(float(world))             # mnist/main.py:127
             e1.record()
             torch.cuda.synchronize()
+            stage("nccl comparison done")
             nccl_ms = max_over_ranks(e0.elapsed_time(e1)) / k
             line["nccl_same_buffer"] = {"ms_per_step": nccl_ms, "bus_gbps_per_rank": S / (nccl_ms / 1e3) * bus_factor(world) / 1e9,
                                         "what": "torch.distributed.all_reduce(SUM) + div_ on one %d-byte buffer" % S}
@@ -420,6 +435,7 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         out.append(row)
         del bufs
         avg.check_status()
+        stage("sweep %d bytes: %s" % (S, {k2: round(v2["us"], 1) for k2, v2 in row.items() if isinstance(v2, dict)}))
     return out
 
 

@@ -198,7 +198,14 @@ int ga_status(ga_ctx *ctx);
 int ga_average_static(int world, int device, const void *const *grad_ptrs, const int64_t *numel,
                       int n_tensors, void *stream, int variant);
 
-/* Frees everything.  Every rank must have finished its last call (barrier first). */
+/*
+ * Tear-down is two collective steps, because an exporter must not free memory that a peer still
+ * has mapped: every rank calls ga_close_peers (unmaps the peers' buckets; the context can no longer
+ * launch), barrier, then every rank calls ga_destroy.  Replaces destroy_process_group for this path.
+ */
+int ga_close_peers(ga_ctx *ctx);
+
+/* Frees everything.  Every rank must have closed its peers first (see ga_close_peers). */
 int ga_destroy(ga_ctx *ctx);
 
 #ifdef __cplusplus

@@ -117,6 +117,8 @@ class GradAverager:
                 import torch.distributed as dist
                 if dist.is_initialized():
                     dist.barrier(group=self._group)   # peers may still be reading my bucket
+                    self._lib.ga_close_peers(self._ctx)
+                    dist.barrier(group=self._group)   # nobody frees memory a peer still has mapped
             self._lib.ga_destroy(self._ctx)
             self._ctx = None
             self._ptr_cache.clear()

@@ -37,6 +37,7 @@ constexpr int kThreads = 512;                  // 16 warps per block
 constexpr int kMaxBlocks = 1024;               // flag rows per rank
 constexpr int kInlineSegs = 128;               // pointer-table entries carried in kernel params
 constexpr int kSegRing = 4;                    // staging slots for larger pointer tables
+constexpr int kHostChunks = 64;                // most chunks one ga_average_host call is cut into
 
 typedef uint4 Vec;
 
@@ -472,6 +473,10 @@ struct ga_ctx {
     int last_blocks, last_threads;
     bool last_was_tensor_call;      // previous launch checks its readers lazily (see ga_drain_kernel)
     const Pad **own_pads_dev;       // device array of the hosted ranks' pads, for ga_drain_kernel
+    // ga_average_host pipeline: copy-in / kernel / copy-out streams and per-chunk events
+    cudaStream_t s_in, s_k, s_out;
+    cudaEvent_t ev_start, ev_done, ev_in[kHostChunks], ev_k[kHostChunks];
+    size_t host_chunk_bytes;
 };
 
 namespace {
@@ -497,6 +502,7 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     if (c->capacity_bytes / kTileBytes > 0xffffffffull) { free(c); return fail(GA_ECAPACITY, "capacity too large"); }
     c->oneshot_max_bytes = world <= 2 ? (size_t)-1 : (size_t)512 << 10;
     c->timeout_ns = 30ull * 1000000000ull;
+    c->host_chunk_bytes = (size_t)8 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
     if (env) c->timeout_ns = strtoull(env, nullptr, 10) * 1000000ull;
 
@@ -555,7 +561,8 @@ int blocks_per_sm(ga_ctx *c, KernelFn fn, int variant) {
 }
 
 // Common launch path.  `segs` (n_local * n_seg entries, rank-major) is nullptr for bucket-direct.
-int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int op, void *stream, int variant, bool direct) {
+int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int op, void *stream, int variant, bool direct,
+           size_t byte_offset = 0) {
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
     if (!c->opened) return fail(GA_ESTATE, "ga_open_peers has not been called");
     if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
@@ -567,8 +574,9 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
 
     Params p;
     memset(&p, 0, sizeof(p));
-    for (int r = 0; r < c->world; ++r) { p.send[r] = c->send_all[r]; p.pad[r] = c->pad_all[r]; }
-    for (int l = 0; l < c->n_local; ++l) p.recv[l] = c->recv[l];
+    // byte_offset: the call works on the sub-bucket [byte_offset, byte_offset + tiles) of every rank
+    for (int r = 0; r < c->world; ++r) { p.send[r] = (char *)c->send_all[r] + byte_offset; p.pad[r] = c->pad_all[r]; }
+    for (int l = 0; l < c->n_local; ++l) p.recv[l] = (char *)c->recv[l] + byte_offset;
     p.status = c->status_dev;
     p.timeout_ns = c->timeout_ns;
     p.n_seg = n_seg;
@@ -634,6 +642,43 @@ int drain_if_needed(ga_ctx *c, void *stream) {
     CUDA_TRY(cudaGetLastError());
     c->launches += 1;
     c->last_was_tensor_call = false;
+    return GA_OK;
+}
+
+int ensure_host_pipeline(ga_ctx *c) {
+    if (c->s_in) return GA_OK;
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->s_in, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->s_k, cudaStreamNonBlocking));
+    CUDA_TRY(cudaStreamCreateWithFlags(&c->s_out, cudaStreamNonBlocking));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_start, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
+    for (int i = 0; i < kHostChunks; ++i) {
+        CUDA_TRY(cudaEventCreateWithFlags(&c->ev_in[i], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->ev_k[i], cudaEventDisableTiming));
+    }
+    return GA_OK;
+}
+
+// Copies the parts of every hosted rank's tensors that fall into bucket bytes [lo, hi) between the
+// host tensors and `dev_base[l] + bucket offset` (to_device) or back (!to_device).
+int copy_chunk(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int n_tensors, size_t lo, size_t hi,
+               bool to_device, cudaStream_t st) {
+    for (int l = 0; l < c->n_local; ++l) {
+        char *dev = to_device ? (char *)c->send_all[c->rank_base + l] : (char *)c->recv[l];
+        size_t off = 0;                                       // bucket offset of tensor i
+        for (int i = 0; i < n_tensors; ++i) {
+            const size_t bytes = (size_t)numel[i] * 4;
+            const size_t a = off > lo ? off : lo;
+            const size_t b = off + bytes < hi ? off + bytes : hi;
+            if (a < b) {
+                char *h = (char *)host_ptrs[(size_t)l * n_tensors + i] + (a - off);
+                if (to_device) CUDA_TRY(cudaMemcpyAsync(dev + a, h, b - a, cudaMemcpyHostToDevice, st));
+                else CUDA_TRY(cudaMemcpyAsync(h, dev + a, b - a, cudaMemcpyDeviceToHost, st));
+            }
+            off += tiles_for_elems(numel[i]) * kTileBytes;
+            if (off >= hi) break;
+        }
+    }
     return GA_OK;
 }
 
@@ -763,26 +808,44 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
     cudaStream_t st = (cudaStream_t)stream;
     rc = drain_if_needed(c, stream);
     if (rc) return rc;
-    for (int l = 0; l < c->n_local; ++l) {
-        size_t off = 0;
-        char *send = (char *)c->send_all[c->rank_base + l];
-        for (int i = 0; i < n_tensors; ++i) {
-            if (numel[i] > 0)
-                CUDA_TRY(cudaMemcpyAsync(send + off, host_ptrs[(size_t)l * n_tensors + i], (size_t)numel[i] * 4, cudaMemcpyHostToDevice, st));
-            off += tiles_for_elems(numel[i]) * kTileBytes;
-        }
+    const size_t bucket_bytes = (size_t)total * kTileBytes;
+    size_t chunk = c->host_chunk_bytes;
+    if ((bucket_bytes + chunk - 1) / chunk > (size_t)kHostChunks)
+        chunk = ((bucket_bytes + kHostChunks - 1) / kHostChunks + kTileBytes - 1) / kTileBytes * kTileBytes;
+    const int n_chunks = (int)((bucket_bytes + chunk - 1) / chunk);
+    if (n_chunks <= 1) {
+        // small set: one H2D pass, one kernel, one D2H pass, all on the caller's stream
+        rc = copy_chunk(c, host_ptrs, numel, n_tensors, 0, bucket_bytes, true, st);
+        if (rc) return rc;
+        rc = launch(c, nullptr, 0, (uint32_t)total, GA_OP_F32_AVG, stream, variant, true);
+        if (rc) return rc;
+        return copy_chunk(c, host_ptrs, numel, n_tensors, 0, bucket_bytes, false, st);
     }
-    rc = launch(c, nullptr, 0, (uint32_t)total, GA_OP_F32_AVG, stream, variant, true);
+    // Large set: cut the bucket into chunks and run copy-in, reduction and copy-out of different
+    // chunks concurrently (PCIe is full duplex), fork/join around the caller's stream.  AUTO is
+    // resolved on the whole set so that every chunk uses the same variant.
+    if (variant == GA_VARIANT_AUTO) variant = ga_pick_variant(c, bucket_bytes);
+    rc = ensure_host_pipeline(c);
     if (rc) return rc;
-    for (int l = 0; l < c->n_local; ++l) {
-        size_t off = 0;
-        const char *recv = (const char *)c->recv[l];
-        for (int i = 0; i < n_tensors; ++i) {
-            if (numel[i] > 0)
-                CUDA_TRY(cudaMemcpyAsync(host_ptrs[(size_t)l * n_tensors + i], recv + off, (size_t)numel[i] * 4, cudaMemcpyDeviceToHost, st));
-            off += tiles_for_elems(numel[i]) * kTileBytes;
-        }
+    CUDA_TRY(cudaEventRecord(c->ev_start, st));
+    CUDA_TRY(cudaStreamWaitEvent(c->s_in, c->ev_start, 0));
+    CUDA_TRY(cudaStreamWaitEvent(c->s_k, c->ev_start, 0));
+    CUDA_TRY(cudaStreamWaitEvent(c->s_out, c->ev_start, 0));
+    for (int k = 0; k < n_chunks; ++k) {
+        const size_t lo = (size_t)k * chunk, hi = lo + chunk < bucket_bytes ? lo + chunk : bucket_bytes;
+        rc = copy_chunk(c, host_ptrs, numel, n_tensors, lo, hi, true, c->s_in);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->ev_in[k], c->s_in));
+        CUDA_TRY(cudaStreamWaitEvent(c->s_k, c->ev_in[k], 0));
+        rc = launch(c, nullptr, 0, (uint32_t)((hi - lo) / kTileBytes), GA_OP_F32_AVG, (void *)c->s_k, variant, true, lo);
+        if (rc) return rc;
+        CUDA_TRY(cudaEventRecord(c->ev_k[k], c->s_k));
+        CUDA_TRY(cudaStreamWaitEvent(c->s_out, c->ev_k[k], 0));
+        rc = copy_chunk(c, host_ptrs, numel, n_tensors, lo, hi, false, c->s_out);
+        if (rc) return rc;
     }
+    CUDA_TRY(cudaEventRecord(c->ev_done, c->s_out));
+    CUDA_TRY(cudaStreamWaitEvent(st, c->ev_done, 0));
     return GA_OK;
 }
 
@@ -848,6 +911,22 @@ int ga_status(ga_ctx *c) {
     return GA_OK;
 }
 
+int ga_close_peers(ga_ctx *c) {
+    if (!c) return GA_OK;
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    for (int r = 0; r < c->world; ++r) {
+        if (c->peer_base[r]) {
+            CUDA_TRY(cudaIpcCloseMemHandle(c->peer_base[r]));
+            c->peer_base[r] = nullptr;
+            c->pad_all[r] = nullptr;
+            c->send_all[r] = nullptr;
+        }
+    }
+    if (c->n_local != c->world) c->opened = false;
+    return GA_OK;
+}
+
 int ga_destroy(ga_ctx *c) {
     if (!c) return GA_OK;
     cudaSetDevice(c->device);
@@ -865,6 +944,11 @@ int ga_destroy(ga_ctx *c) {
     }
     if (c->status_host) cudaFreeHost(c->status_host);
     if (c->own_pads_dev) cudaFree(c->own_pads_dev);
+    if (c->s_in) {
+        cudaStreamDestroy(c->s_in); cudaStreamDestroy(c->s_k); cudaStreamDestroy(c->s_out);
+        cudaEventDestroy(c->ev_start); cudaEventDestroy(c->ev_done);
+        for (int i = 0; i < kHostChunks; ++i) { cudaEventDestroy(c->ev_in[i]); cudaEventDestroy(c->ev_k[i]); }
+    }
     free(c);
     return GA_OK;
 }

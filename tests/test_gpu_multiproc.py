@@ -16,8 +16,17 @@ def _run(world, backend):
     port = free_port()
     procs = [ctx.Process(target=ipc_world, args=(r, world, port, q, backend)) for r in range(world)]
     [p.start() for p in procs]
-    res = [q.get(timeout=600) for _ in procs]
-    [p.join(60) for p in procs]
+    res = []
+    try:
+        for _ in procs:
+            res.append(q.get(timeout=240))
+            if res[-1]["fail"]:
+                break                                   # one rank failed: the others may be stuck in a collective
+    finally:
+        for p in procs:
+            p.join(5 if (res and res[-1]["fail"]) or len(res) < len(procs) else 60)
+            if p.is_alive():
+                p.terminate()
     for d in res:
         assert not d["fail"], d["fail"]
         assert d["launches"] > 200
