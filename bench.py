@@ -174,7 +174,11 @@ def algorithmic_hbm_bytes(world, nbytes, variant_name, hosted):
     ranks (kernel table): pack 2S; one-shot: read W*S, write S; two-shot: reduce-scatter
     read S + write 2S/W, all-gather read + write (W-1)S/W each."""
     s, w = float(nbytes), world
-    per_rank = (w + 3) * s if variant_name == "oneshot" else 5.0 * s
+    per_rank = {"oneshot": (w + 3) * s,                       # pack 2S, read W*S, write S
+                "twoshot": 5.0 * s,                           # pack 2S, RS read S + write 2S/W, AG read+write (W-1)S/W each
+                "oneshot_push": (2 * w + 2) * s,              # read S, write W*S staging, read W*S, write S
+                "twoshot_push": (4.0 + 2.0 * (w - 1) / w) * s  # read S, write S, read S, write S (grads+gather), unpack 2(W-1)S/W
+                }[variant_name]
     return per_rank * hosted
 
 
@@ -186,7 +190,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bytes", type=int, default=DEFAULT_BYTES, help="gradient bytes per rank")
     ap.add_argument("--world", type=int, default=0, help="world size when --gpus 1 (default 4)")
-    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot", "oneshot_push", "twoshot_push"])
     ap.add_argument("--no-extras", action="store_true", help="skip the sweep / MNIST / cpu_baseline legs")
     ap.add_argument("--sweep", action="store_true", help="N > 1: size sweep 4 KB..1 GB, ours (both variants, fused and bucket) vs NCCL")
     ap.add_argument("--sweep-max", type=int, default=1 << 30)
@@ -222,8 +226,10 @@ def main():
     dev = torch.device("cuda", torch.cuda.current_device())
     S = args.bytes - args.bytes % 4
     n = S // 4
-    variant_id = {"auto": avg.pick_variant(S), "oneshot": ga.ONESHOT, "twoshot": ga.TWOSHOT}[args.variant]
-    variant_name = "oneshot" if variant_id == ga.ONESHOT else "twoshot"
+    names = {ga.ONESHOT: "oneshot", ga.TWOSHOT: "twoshot", ga.ONESHOT_PUSH: "oneshot_push", ga.TWOSHOT_PUSH: "twoshot_push"}
+    variant_id = {"auto": avg.pick_variant(S), "oneshot": ga.ONESHOT, "twoshot": ga.TWOSHOT,
+                  "oneshot_push": ga.ONESHOT_PUSH, "twoshot_push": ga.TWOSHOT_PUSH}[args.variant]
+    variant_name = names[variant_id]
 
     # gradient sets: rotate so that consecutive steps never find their inputs in L2
     n_sets = max(2, min(64, -(-(300 << 20) // (hosted * S))))
@@ -292,8 +298,8 @@ def main():
         roofline = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                     "traffic": load_traffic(), "kernel": "ga_fused_kernel<%d,%s,f32avg>" % (world, variant_name),
                     "kernel_ms": kernel_ms, "peak_source": peak_src,
-                    "algorithmic": "%d hosted ranks x %s x S bytes per launch (DESIGN.md kernel table)"
-                                   % (hosted, "(W+3)" if variant_name == "oneshot" else "5")}
+                    "algorithmic": "%d hosted ranks x %.2f x S bytes per launch (DESIGN.md kernel table)"
+                                   % (hosted, alg_bytes / hosted / S)}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
@@ -359,8 +365,8 @@ def main():
     if sampler is not None:
         line["clocks"] = sampler.stop(windows)
 
-    if not args.profile and not args.no_extras and rank == 0:
-        # CPU leg last, GPU idle: the reference's averaging on host cores, bounded sample
+    if not args.profile and not args.no_extras and rank == 0 and not multi:
+        # CPU leg last, GPU idle, N = 1 only: the reference's averaging on host cores, bounded sample
         line["cpu_baseline"] = cpu_reference(world, S, steps=12, warmup=2, budget_s=20.0)
 
     if multi:
@@ -409,8 +415,11 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         bufs = [torch.randn(n, device=dev) for _ in range(2 if S >= (32 << 20) else 8)]
         k = [0]
         row = {"bytes": S}
-        for vname, v in (("oneshot", ga.ONESHOT), ("twoshot", ga.TWOSHOT)):
-            if vname == "oneshot" and S > (64 << 20) and world > 2:
+        for vname, v in (("oneshot", ga.ONESHOT), ("twoshot", ga.TWOSHOT), ("oneshot_push", ga.ONESHOT_PUSH),
+                         ("twoshot_push", ga.TWOSHOT_PUSH)):
+            if vname.startswith("oneshot") and S > (64 << 20) and world > 2:
+                continue
+            if vname == "oneshot_push" and S * world > avg.capacity:
                 continue
 
             def fused():
@@ -418,6 +427,8 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
                 avg.all_reduce_([[bufs[k[0] % len(bufs)]]], average=True, variant=v)
             med, best = timed(fused, iters)
             row["fused_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+            if vname.endswith("_push"):
+                continue
             avg.bucket_acquire()
 
             def bucket():

@@ -50,6 +50,9 @@ extern "C" {
 #define GA_VARIANT_AUTO     0   /* chosen from the byte count, see ga_set_option(GA_OPT_ONESHOT_MAX_BYTES) */
 #define GA_VARIANT_ONESHOT  1   /* every rank reads all `world` buckets: 1 barrier, (world-1)*S ingress */
 #define GA_VARIANT_TWOSHOT  2   /* reduce-scatter + all-gather by peer reads: 2 barriers, 2(world-1)/world*S */
+#define GA_VARIANT_ONESHOT_PUSH 3 /* every rank STORES its set into every peer's staging slot, local fold   */
+#define GA_VARIANT_TWOSHOT_PUSH 4 /* scatter to shard owners by remote stores, owner folds, result stored to
+                                     every peer's gather region; pack folds into the scatter (tensor calls) */
 
 /* element type + operation */
 #define GA_OP_F32_AVG   0   /* fp32: rank-order sum, then / (float)world      mnist/main.py:126-127 */

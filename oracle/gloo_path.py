@@ -43,7 +43,17 @@ def free_port():
         return s.getsockname()[1]
 
 
+_LAUNCHER_ENV = ("TORCHELASTIC_USE_AGENT_STORE", "TORCHELASTIC_RUN_ID", "TORCHELASTIC_RESTART_COUNT",
+                 "TORCHELASTIC_MAX_RESTARTS", "RANK", "LOCAL_RANK", "WORLD_SIZE", "LOCAL_WORLD_SIZE", "GROUP_RANK",
+                 "ROLE_RANK", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS")
+
+
 def _worker(rank, world, port, fn, args, out_dir, threads):
+    # When the parent runs under torchrun its variables leak into this CPU world; with
+    # TORCHELASTIC_USE_AGENT_STORE set, rank 0 would wait for an agent-owned store instead of
+    # serving tcp://127.0.0.1:port itself and every rank would hang.
+    for k in _LAUNCHER_ENV:
+        os.environ.pop(k, None)
     torch.set_num_threads(threads)
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
     try:

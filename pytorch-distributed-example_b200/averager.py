@@ -10,8 +10,11 @@ from . import _lib
 from ._lib import GradAvgError, check, load_library
 
 AUTO, ONESHOT, TWOSHOT = _lib.VARIANT_AUTO, _lib.VARIANT_ONESHOT, _lib.VARIANT_TWOSHOT
+ONESHOT_PUSH, TWOSHOT_PUSH = _lib.VARIANT_ONESHOT_PUSH, _lib.VARIANT_TWOSHOT_PUSH
 _VARIANTS = {"auto": AUTO, "oneshot": ONESHOT, "1shot": ONESHOT, "twoshot": TWOSHOT, "2shot": TWOSHOT,
-             AUTO: AUTO, ONESHOT: ONESHOT, TWOSHOT: TWOSHOT, None: AUTO}
+             "oneshot_push": ONESHOT_PUSH, "twoshot_push": TWOSHOT_PUSH,
+             AUTO: AUTO, ONESHOT: ONESHOT, TWOSHOT: TWOSHOT, ONESHOT_PUSH: ONESHOT_PUSH, TWOSHOT_PUSH: TWOSHOT_PUSH,
+             None: AUTO}
 
 
 def _tiles(numel):

@@ -60,6 +60,7 @@ struct Params {
     void *send[kMaxWorld];      // every rank's bucket, by global rank (peer-mapped)
     Pad *pad[kMaxWorld];        // every rank's flag pad, by global rank (peer-mapped)
     void *recv[kMaxWorld];      // result regions of the hosted ranks, by local index
+    void *gather[kMaxWorld];    // every rank's gather region, by global rank (push variants write into it)
     const Seg *dev_segs;        // [n_local][n_seg], or nullptr -> inline_segs
     int *status;                // host-mapped error word
     unsigned long long timeout_ns;
@@ -392,6 +393,178 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// push variants: the same averaging with remote STORES instead of remote loads
+// ------------------------------------------------------------------------------------------
+// NVLink writes are posted (no request/response round trip), and pack folds into the transfer:
+// a gradient tile is read once from the tensor and stored straight into the owner's staging slot.
+//   two-shot push: (1) scatter: tile i of shard j -> rank j's staging slot [me]      (remote stores)
+//                  (2) flags    (3) rank j folds its W slots in rank order, divides, writes its own
+//                  gradients and stores the result into every peer's gather region   (remote stores)
+//                  (4) flags    (5) unpack the other shards from my gather region    (local)
+//   one-shot push: (1) every tile -> every rank's staging slot [me]  (2) flags  (3) local fold
+// The staging area is the bucket (`send`), slot s at s * slot_tiles; the gather region sits behind
+// it in the same IPC allocation.  Tensor-list calls only.
+template <int W, int OP, typename SrcFn, typename OutFn>
+__device__ __forceinline__ void fold_tile(SrcFn src, float wf, int lane, OutFn out) {
+    constexpr int NB = Batch<W>::value;
+#pragma unroll
+    for (int u0 = 0; u0 < kLaneVecs; u0 += NB) {
+        Vec v[W][NB];
+#pragma unroll
+        for (int r = 0; r < W; ++r) {
+            const Vec *s = src(r) + lane;
+#pragma unroll
+            for (int u = 0; u < NB; ++u) v[r][u] = __ldcg(s + (u0 + u) * 32);
+        }
+        Vec acc[NB];
+#pragma unroll
+        for (int u = 0; u < NB; ++u) {
+            acc[u] = v[0][u];
+#pragma unroll
+            for (int r = 1; r < W; ++r) {          // ((g0 + g1) + g2) + ...
+                acc[u].x = ElemOp<OP>::add(acc[u].x, v[r][u].x);
+                acc[u].y = ElemOp<OP>::add(acc[u].y, v[r][u].y);
+                acc[u].z = ElemOp<OP>::add(acc[u].z, v[r][u].z);
+                acc[u].w = ElemOp<OP>::add(acc[u].w, v[r][u].w);
+            }
+            acc[u].x = ElemOp<OP>::fin(acc[u].x, wf);
+            acc[u].y = ElemOp<OP>::fin(acc[u].y, wf);
+            acc[u].z = ElemOp<OP>::fin(acc[u].z, wf);
+            acc[u].w = ElemOp<OP>::fin(acc[u].w, wf);
+        }
+        out(u0, acc);
+    }
+}
+
+template <int W, int VARIANT, int OP>
+__global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_constant__ Params p) {
+    __shared__ int s_abort;
+    __shared__ int s_last;
+    constexpr int NB = Batch<W>::value;
+    const int ly = blockIdx.y;
+    const int r = p.rank_base + ly;
+    const int b = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpb = blockDim.x >> 5;
+    const uint32_t stride = gridDim.x * wpb;
+    const uint32_t first = b * wpb + warp;
+    const uint32_t T = p.total_tiles;
+    const uint32_t Ts = VARIANT == GA_VARIANT_ONESHOT_PUSH ? T : p.shard_tiles;   // tiles per staging slot
+    const float wf = (float)W;
+
+    Pad *mypad = p.pad[r];
+    Vec *mystage = (Vec *)p.send[r];
+    Vec *mygather = (Vec *)p.gather[r];
+    Sink sink;
+    sink.n_seg = (int)p.n_seg;
+    sink.segs = (p.dev_segs ? p.dev_segs : p.inline_segs) + (size_t)ly * p.n_seg;
+    sink.recv = nullptr;
+
+    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
+    __syncthreads();
+
+    // (0) every rank must have consumed the staging data of the previous call before anyone
+    //     stores into it again (needed after a one-shot call; free when the ranks are in step)
+    if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+
+    // (1) scatter my gradient tiles into the owners' staging slots, nearest rank first
+    if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
+        for (uint32_t t = first; t < T; t += stride) {
+            const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+            Vec v[kLaneVecs];
+            load_grad_tile(sg, t, lane, v);
+#pragma unroll
+            for (int jj = 0; jj < W; ++jj) {
+                const int j = (r + jj) % W;
+                Vec *dst = (Vec *)p.send[j] + ((size_t)r * Ts + t) * kTileVecs + lane;
+#pragma unroll
+                for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+            }
+        }
+    } else {
+        for (uint32_t i = first; i < Ts; i += stride) {
+#pragma unroll 1
+            for (int jj = 0; jj < W; ++jj) {
+                const int j = (r + jj) % W;
+                const uint32_t t = j * Ts + i;
+                if (t >= T) continue;
+                const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+                Vec v[kLaneVecs];
+                load_grad_tile(sg, t, lane, v);
+                Vec *dst = (Vec *)p.send[j] + ((size_t)r * Ts + i) * kTileVecs + lane;
+#pragma unroll
+                for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+            }
+        }
+    }
+
+    // (2) my column has landed everywhere / wait for everyone's column
+    const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
+    raise_flags<W>(p, ready_off, p.epoch);
+    if (!wait_flags<W>(mypad->ready[b], p.epoch, p, &s_abort)) return;
+
+    if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
+        // (3) fold the W local slots of every tile straight into the gradient tensors
+        for (uint32_t t = first; t < T; t += stride) {
+            const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+            fold_tile<W, OP>([&](int s) { return mystage + ((size_t)s * Ts + t) * kTileVecs; }, wf, lane,
+                             [&](int u0, const Vec(&acc)[NB]) { store_grad_vecs<NB>(sg, t, lane, u0, acc); });
+        }
+    } else {
+        // (3) fold my shard from the W local slots; result -> my gradients and every peer's gather region
+        for (uint32_t i = first; i < Ts; i += stride) {
+            const uint32_t t = r * Ts + i;
+            if (t >= T) break;
+            const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+            fold_tile<W, OP>([&](int s) { return mystage + ((size_t)s * Ts + i) * kTileVecs; }, wf, lane,
+                             [&](int u0, const Vec(&acc)[NB]) {
+                                 store_grad_vecs<NB>(sg, t, lane, u0, acc);
+#pragma unroll
+                                 for (int jj = 1; jj < W; ++jj) {
+                                     const int j = (r + jj) % W;
+                                     Vec *dst = (Vec *)p.gather[j] + (size_t)t * kTileVecs + u0 * 32 + lane;
+#pragma unroll
+                                     for (int u = 0; u < NB; ++u) __stcg(dst + u * 32, acc[u]);
+                                 }
+                             });
+        }
+        // (4) my reduced column has landed everywhere / wait for everyone's
+        const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
+        raise_flags<W>(p, mid_off, p.epoch);
+        if (!wait_flags<W>(mypad->mid[b], p.epoch, p, &s_abort)) return;
+        // (5) unpack the other ranks' shards from my gather region (local traffic only)
+        for (uint32_t i = first; i < Ts; i += stride) {
+#pragma unroll 1
+            for (int jj = 1; jj < W; ++jj) {
+                const int j = (r + jj) % W;
+                const uint32_t t = j * Ts + i;
+                if (t >= T) continue;
+                const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
+                const Vec *src = mygather + (size_t)t * kTileVecs + lane;
+                Vec v[kLaneVecs];
+#pragma unroll
+                for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcg(src + u * 32);
+                store_grad_vecs<kLaneVecs>(sg, t, lane, 0, v);
+            }
+        }
+    }
+
+    // (6) this rank is done with its staging and gather data
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x == 0) mypad->finished_blocks = 0;
+        const size_t done_off = offsetof(Pad, done) / 4 + r;
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch);
+    }
+}
+
 // Launched only when a bucket-direct call follows a tensor-list call: the caller is about to
 // overwrite the bucket from the host side of the stream, so every peer must have finished
 // reading it (tensor-list calls check this lazily, at the start of the NEXT kernel).
@@ -430,8 +603,18 @@ template <int W, int VARIANT> KernelFn pick_op(int op) {
            : op == GA_OP_F32_SUM ? (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_F32_SUM>
                                  : (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_F32_AVG>;
 }
+template <int W, int VARIANT> KernelFn pick_push_op(int op) {
+    return op == GA_OP_I32_SUM   ? (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_I32_SUM>
+           : op == GA_OP_F32_SUM ? (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_SUM>
+                                 : (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_AVG>;
+}
 template <int W> KernelFn pick_variant(int variant, int op) {
-    return variant == GA_VARIANT_TWOSHOT ? pick_op<W, GA_VARIANT_TWOSHOT>(op) : pick_op<W, GA_VARIANT_ONESHOT>(op);
+    switch (variant) {
+        case GA_VARIANT_TWOSHOT: return pick_op<W, GA_VARIANT_TWOSHOT>(op);
+        case GA_VARIANT_ONESHOT_PUSH: return pick_push_op<W, GA_VARIANT_ONESHOT_PUSH>(op);
+        case GA_VARIANT_TWOSHOT_PUSH: return pick_push_op<W, GA_VARIANT_TWOSHOT_PUSH>(op);
+    }
+    return pick_op<W, GA_VARIANT_ONESHOT>(op);
 }
 KernelFn pick_kernel(int world, int variant, int op) {
     switch (world) {
@@ -456,10 +639,11 @@ struct ga_ctx {
     void *recv[kMaxWorld];          // own result regions, by local index
     void *peer_base[kMaxWorld];     // IPC-opened peer allocations, by global rank (nullptr = not opened)
     void *send_all[kMaxWorld];      // by global rank
+    void *gather_all[kMaxWorld];    // by global rank (second half of the IPC allocation)
     Pad *pad_all[kMaxWorld];        // by global rank
     bool opened, broken;
     uint32_t epoch;                 // epoch of the last launch
-    int sm_count, blocks_per_sm[2][kMaxWorld + 1];   // unused slots stay 0
+    int sm_count, blocks_per_sm[8];                  // by variant; 0 = not queried yet
     int max_blocks_opt;
     size_t oneshot_max_bytes;
     unsigned long long timeout_ns;
@@ -511,11 +695,12 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->sm_count = prop.multiProcessorCount;
 
     for (int l = 0; l < n_local; ++l) {
-        CUDA_TRY(cudaMalloc(&c->base[l], kPadBytes + c->capacity_bytes));
+        CUDA_TRY(cudaMalloc(&c->base[l], kPadBytes + 2 * c->capacity_bytes));
         CUDA_TRY(cudaMemset(c->base[l], 0, kPadBytes));
         CUDA_TRY(cudaMalloc(&c->recv[l], c->capacity_bytes));
         c->pad_all[rank_base + l] = (Pad *)c->base[l];
         c->send_all[rank_base + l] = (char *)c->base[l] + kPadBytes;
+        c->gather_all[rank_base + l] = (char *)c->base[l] + kPadBytes + c->capacity_bytes;
     }
     CUDA_TRY(cudaHostAlloc((void **)&c->status_host, sizeof(int), cudaHostAllocMapped));
     *c->status_host = 0;
@@ -551,7 +736,7 @@ int ensure_seg_ring(ga_ctx *c, size_t entries) {
 }
 
 int blocks_per_sm(ga_ctx *c, KernelFn fn, int variant) {
-    int &cached = c->blocks_per_sm[variant == GA_VARIANT_TWOSHOT][c->world];
+    int &cached = c->blocks_per_sm[variant];
     if (cached == 0) {
         int n = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, (const void *)fn, kThreads, 0) != cudaSuccess || n < 1) n = 1;
@@ -567,15 +752,25 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     if (!c->opened) return fail(GA_ESTATE, "ga_open_peers has not been called");
     if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
     if (variant == GA_VARIANT_AUTO) variant = ga_pick_variant(c, (size_t)total_tiles * kTileBytes);
-    if (variant != GA_VARIANT_ONESHOT && variant != GA_VARIANT_TWOSHOT) return fail(GA_EINVAL, "unknown variant %d", variant);
+    if (variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_TWOSHOT_PUSH) return fail(GA_EINVAL, "unknown variant %d", variant);
     if (total_tiles == 0) return GA_OK;    // nothing to average: no launch, epoch unchanged on every rank
+    // Bucket-direct calls exist in the pull form only (their input already sits in the bucket).
+    if (direct && variant == GA_VARIANT_ONESHOT_PUSH) variant = GA_VARIANT_ONESHOT;
+    if (direct && variant == GA_VARIANT_TWOSHOT_PUSH) variant = GA_VARIANT_TWOSHOT;
+    // One-shot push stages W copies of the set in every rank's bucket; beyond that, two-shot push.
+    if (variant == GA_VARIANT_ONESHOT_PUSH && (size_t)total_tiles * kTileBytes * c->world > c->capacity_bytes)
+        variant = GA_VARIANT_TWOSHOT_PUSH;
     CUDA_TRY(cudaSetDevice(c->device));
     cudaStream_t st = (cudaStream_t)stream;
 
     Params p;
     memset(&p, 0, sizeof(p));
     // byte_offset: the call works on the sub-bucket [byte_offset, byte_offset + tiles) of every rank
-    for (int r = 0; r < c->world; ++r) { p.send[r] = (char *)c->send_all[r] + byte_offset; p.pad[r] = c->pad_all[r]; }
+    for (int r = 0; r < c->world; ++r) {
+        p.send[r] = (char *)c->send_all[r] + byte_offset;
+        p.gather[r] = c->gather_all[r];
+        p.pad[r] = c->pad_all[r];
+    }
     for (int l = 0; l < c->n_local; ++l) p.recv[l] = (char *)c->recv[l] + byte_offset;
     p.status = c->status_dev;
     p.timeout_ns = c->timeout_ns;
@@ -606,7 +801,8 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
 
     KernelFn fn = pick_kernel(c->world, variant, op);
     // Grid: one warp per tile slot, at most what is co-resident (blocks spin on peers' flags).
-    const uint32_t slots = variant == GA_VARIANT_TWOSHOT ? p.shard_tiles : total_tiles;
+    const bool two_shot = variant == GA_VARIANT_TWOSHOT || variant == GA_VARIANT_TWOSHOT_PUSH;
+    const uint32_t slots = two_shot ? p.shard_tiles : total_tiles;
     const int wpb = kThreads / 32;
     int resident = blocks_per_sm(c, fn, variant) * c->sm_count / c->n_local;
     if (resident > kMaxBlocks) resident = kMaxBlocks;
@@ -736,6 +932,7 @@ int ga_open_peers(ga_ctx *c, const unsigned char *handles) {
         c->peer_base[r] = ptr;
         c->pad_all[r] = (Pad *)ptr;
         c->send_all[r] = (char *)ptr + kPadBytes;
+        c->gather_all[r] = (char *)ptr + kPadBytes + c->capacity_bytes;
     }
     c->opened = true;
     return GA_OK;
@@ -921,6 +1118,7 @@ int ga_close_peers(ga_ctx *c) {
             c->peer_base[r] = nullptr;
             c->pad_all[r] = nullptr;
             c->send_all[r] = nullptr;
+            c->gather_all[r] = nullptr;
         }
     }
     if (c->n_local != c->world) c->opened = false;

@@ -17,7 +17,8 @@ import oracle
 
 pytestmark = pytest.mark.gpu
 
-ONESHOT, TWOSHOT = 1, 2
+ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH = 1, 2, 3, 4
+ALL_VARIANTS = (ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH)
 F32_AVG, I32_SUM, F32_SUM = 0, 1, 2
 
 
@@ -86,7 +87,7 @@ def _assert_all_ranks_equal(dev, want, what):
 
 
 @pytest.mark.parametrize("world", [1, 2, 3, 4, 5, 8])
-@pytest.mark.parametrize("variant", [ONESHOT, TWOSHOT])
+@pytest.mark.parametrize("variant", ALL_VARIANTS)
 @pytest.mark.parametrize("set_name", ["mini", "mnist"])
 def test_bit_exact_vs_fold(lib, world, variant, set_name):
     shapes = oracle.MINI_SHAPES if set_name == "mini" else oracle.MNIST_CNN_SHAPES
@@ -110,7 +111,7 @@ def test_golden_mnist_sha(lib, golden_dir, world):
         host = _host_sets(oracle.MNIST_CNN_SHAPES, world, gen)
         w = LocalWorld(lib, world, 4 << 20)
         try:
-            for variant in (ONESHOT, TWOSHOT):
+            for variant in ALL_VARIANTS:
                 dev = _to_dev(host)
                 w.tensors(dev, variant=variant)
                 flat = np.concatenate([t.cpu().numpy().ravel() for t in dev[0]])
@@ -133,7 +134,7 @@ def test_golden_mini_vs_reference_gloo(lib, golden_dir, world):
     ref = [z["out_t%d" % i] for i in range(n)]
     w = LocalWorld(lib, world, 1 << 20)
     try:
-        for variant in (ONESHOT, TWOSHOT):
+        for variant in ALL_VARIANTS:
             dev = _to_dev(host)
             w.tensors(dev, variant=variant)
             for i in range(n):
@@ -158,7 +159,7 @@ def test_edge_cases(lib):
         st = ctypes.c_void_p(0)
         _check(lib, lib.ga_average(w.ctx, None, None, 0, st, ONESHOT))
         sizes = [0, 1, 2, 3, 4, 5, 511, 512, 513, 1023, 1025, 0, 7, 4096 + 3]
-        for variant in (ONESHOT, TWOSHOT):
+        for variant in ALL_VARIANTS:
             host = [[np.random.default_rng(100 * r + i).standard_normal(s).astype(np.float32)
                      for i, s in enumerate(sizes)] for r in range(world)]
             want = _fold(host, world)
@@ -198,7 +199,7 @@ def test_special_values(lib):
     want = _fold(host, world)[0]
     w = LocalWorld(lib, world, 1 << 20)
     try:
-        for variant in (ONESHOT, TWOSHOT):
+        for variant in ALL_VARIANTS:
             dev = _to_dev(host)
             w.tensors(dev, variant=variant)
             got = dev[1][0].cpu().numpy()
@@ -233,7 +234,7 @@ def test_int32_sum_toy(lib, golden_dir):
     want = oracle.fold_sum_i32_c([host[r][0] for r in range(world)])
     w = LocalWorld(lib, world, 1 << 20)
     try:
-        for variant in (ONESHOT, TWOSHOT):
+        for variant in ALL_VARIANTS:
             dev = _to_dev(host)
             w.tensors(dev, op=I32_SUM, variant=variant)
             for r in range(world):
@@ -290,7 +291,7 @@ def test_repeated_steps_changing_pointers(lib):
         st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
         for step in range(300):
             shapes = sets[step % len(sets)]
-            variant = ONESHOT if (step // 2) % 2 == 0 else TWOSHOT
+            variant = ALL_VARIANTS[(step // 2) % 4]
             dev = [[torch.randn(s, device="cuda", generator=None) for s in shapes] for _ in range(world)]
             if step % 50 == 0:
                 expected.append((step, [[t.cpu().numpy().copy() for t in rank] for rank in dev]))
@@ -355,7 +356,7 @@ def test_full_size_properties(lib):
         base = [torch.randn(n, device="cuda", generator=g) for _ in range(world)]
         host = [b.cpu().numpy() for b in base]
         want = oracle.fold_average_c(host)
-        for variant in (ONESHOT, TWOSHOT):
+        for variant in ALL_VARIANTS:
             dev = [[b.clone()] for b in base]
             w.tensors(dev, variant=variant)
             got0 = dev[0][0].cpu().numpy()
@@ -379,7 +380,7 @@ def test_resnet18_set(lib):
     want = _fold(host, world)
     w = LocalWorld(lib, world, 48 << 20)
     try:
-        for variant in (ONESHOT, TWOSHOT):
+        for variant in ALL_VARIANTS:
             dev = [[t.clone() for t in rank] for rank in base]
             w.tensors(dev, variant=variant)
             _assert_all_ranks_equal(dev, want, "resnet18 v=%d" % variant)
