@@ -635,6 +635,7 @@ KernelFn pick_kernel(int world, int variant, int op) {
 struct ga_ctx {
     int world, rank_base, n_local, device;
     size_t capacity_bytes;          // per rank, multiple of kTileBytes
+    size_t region_bytes;            // capacity + slack: two-shot push stages world * ceil(T / world) >= T tiles
     void *base[kMaxWorld];          // own allocations [Pad | bucket], by local index
     void *recv[kMaxWorld];          // own result regions, by local index
     void *peer_base[kMaxWorld];     // IPC-opened peer allocations, by global rank (nullptr = not opened)
@@ -684,6 +685,7 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->world = world; c->rank_base = rank_base; c->n_local = n_local; c->device = device;
     c->capacity_bytes = (capacity_bytes + kTileBytes - 1) / kTileBytes * kTileBytes;
     if (c->capacity_bytes / kTileBytes > 0xffffffffull) { free(c); return fail(GA_ECAPACITY, "capacity too large"); }
+    c->region_bytes = c->capacity_bytes + (size_t)kMaxWorld * kTileBytes;
     c->oneshot_max_bytes = world <= 2 ? (size_t)-1 : (size_t)512 << 10;
     c->timeout_ns = 30ull * 1000000000ull;
     c->host_chunk_bytes = (size_t)8 << 20;
@@ -695,12 +697,12 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->sm_count = prop.multiProcessorCount;
 
     for (int l = 0; l < n_local; ++l) {
-        CUDA_TRY(cudaMalloc(&c->base[l], kPadBytes + 2 * c->capacity_bytes));
+        CUDA_TRY(cudaMalloc(&c->base[l], kPadBytes + 2 * c->region_bytes));
         CUDA_TRY(cudaMemset(c->base[l], 0, kPadBytes));
         CUDA_TRY(cudaMalloc(&c->recv[l], c->capacity_bytes));
         c->pad_all[rank_base + l] = (Pad *)c->base[l];
         c->send_all[rank_base + l] = (char *)c->base[l] + kPadBytes;
-        c->gather_all[rank_base + l] = (char *)c->base[l] + kPadBytes + c->capacity_bytes;
+        c->gather_all[rank_base + l] = (char *)c->base[l] + kPadBytes + c->region_bytes;
     }
     CUDA_TRY(cudaHostAlloc((void **)&c->status_host, sizeof(int), cudaHostAllocMapped));
     *c->status_host = 0;
@@ -932,7 +934,7 @@ int ga_open_peers(ga_ctx *c, const unsigned char *handles) {
         c->peer_base[r] = ptr;
         c->pad_all[r] = (Pad *)ptr;
         c->send_all[r] = (char *)ptr + kPadBytes;
-        c->gather_all[r] = (char *)ptr + kPadBytes + c->capacity_bytes;
+        c->gather_all[r] = (char *)ptr + kPadBytes + c->region_bytes;
     }
     c->opened = true;
     return GA_OK;

@@ -189,6 +189,26 @@ def test_edge_cases(lib):
         w.close()
 
 
+@pytest.mark.parametrize("world", [3, 4, 8])
+def test_exact_capacity(lib, world):
+    """Bucket capacity == bytes of the set (what the Python layer allocates on first use): the
+    two-shot staging layout needs world * ceil(T / world) >= T tiles and must not spill."""
+    shapes = oracle.MNIST_CNN_SHAPES
+    numel = (ctypes.c_int64 * len(shapes))(*oracle.numel_of(shapes))
+    need = lib.ga_bucket_offset(numel, len(shapes), len(shapes))
+    host = _host_sets(shapes, world)
+    want = _fold(host, world)
+    w = LocalWorld(lib, world, need)
+    try:
+        for rep in range(3):
+            for variant in ALL_VARIANTS:
+                dev = _to_dev(host)
+                w.tensors(dev, variant=variant)
+                _assert_all_ranks_equal(dev, want, "exact capacity ws=%d v=%d" % (world, variant))
+    finally:
+        w.close()
+
+
 def test_special_values(lib):
     """inf / nan / denormals / signed zero go through the same IEEE adds and divide as the fold."""
     world = 3
