@@ -177,7 +177,8 @@ def algorithmic_hbm_bytes(world, nbytes, variant_name, hosted):
     per_rank = {"oneshot": (w + 3) * s,                       # pack 2S, read W*S, write S
                 "twoshot": 5.0 * s,                           # pack 2S, RS read S + write 2S/W, AG read+write (W-1)S/W each
                 "oneshot_push": (2 * w + 2) * s,              # read S, write W*S staging, read W*S, write S
-                "twoshot_push": (4.0 + 2.0 * (w - 1) / w) * s  # read S, write S, read S, write S (grads+gather), unpack 2(W-1)S/W
+                "twoshot_push": (4.0 + 2.0 * (w - 1) / w) * s,  # read S, write S, read S, write S (grads+gather), unpack 2(W-1)S/W
+                "twoshot_pipe": (4.0 + 2.0 * (w - 1) / w) * s
                 }[variant_name]
     return per_rank * hosted
 
@@ -190,10 +191,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bytes", type=int, default=DEFAULT_BYTES, help="gradient bytes per rank")
     ap.add_argument("--world", type=int, default=0, help="world size when --gpus 1 (default 4)")
-    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot", "oneshot_push", "twoshot_push"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot", "oneshot_push", "twoshot_push", "twoshot_pipe"])
     ap.add_argument("--no-extras", action="store_true", help="skip the sweep / MNIST / cpu_baseline legs")
     ap.add_argument("--sweep", action="store_true", help="N > 1: size sweep 4 KB..1 GB, ours (both variants, fused and bucket) vs NCCL")
     ap.add_argument("--sweep-max", type=int, default=1 << 30)
+    ap.add_argument("--explore", action="store_true", help="N > 1: tuning grid for the pipelined variant (group x blocks)")
     ap.add_argument("--profile", action="store_true", help="bare loop for ncu: no extras, no cpu leg, no e2e")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -226,9 +228,11 @@ def main():
     dev = torch.device("cuda", torch.cuda.current_device())
     S = args.bytes - args.bytes % 4
     n = S // 4
-    names = {ga.ONESHOT: "oneshot", ga.TWOSHOT: "twoshot", ga.ONESHOT_PUSH: "oneshot_push", ga.TWOSHOT_PUSH: "twoshot_push"}
+    names = {ga.ONESHOT: "oneshot", ga.TWOSHOT: "twoshot", ga.ONESHOT_PUSH: "oneshot_push", ga.TWOSHOT_PUSH: "twoshot_push",
+             ga.TWOSHOT_PIPE: "twoshot_pipe"}
     variant_id = {"auto": avg.pick_variant(S), "oneshot": ga.ONESHOT, "twoshot": ga.TWOSHOT,
-                  "oneshot_push": ga.ONESHOT_PUSH, "twoshot_push": ga.TWOSHOT_PUSH}[args.variant]
+                  "oneshot_push": ga.ONESHOT_PUSH, "twoshot_push": ga.TWOSHOT_PUSH,
+                  "twoshot_pipe": ga.TWOSHOT_PIPE}[args.variant]
     variant_name = names[variant_id]
 
     # gradient sets: rotate so that consecutive steps never find their inputs in L2
@@ -361,6 +365,8 @@ def main():
             line["extras"] = extras_single_gpu(avg, world, dev)
         if multi and args.sweep:
             line["sweep"] = sweep_multi(avg, world, dev, dist, args.sweep_max)
+        if multi and args.explore:
+            line["explore"] = explore_pipe(avg, world, dev, dist)
 
     if sampler is not None:
         line["clocks"] = sampler.stop(windows)
@@ -416,7 +422,7 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         k = [0]
         row = {"bytes": S}
         for vname, v in (("oneshot", ga.ONESHOT), ("twoshot", ga.TWOSHOT), ("oneshot_push", ga.ONESHOT_PUSH),
-                         ("twoshot_push", ga.TWOSHOT_PUSH)):
+                         ("twoshot_push", ga.TWOSHOT_PUSH), ("twoshot_pipe", ga.TWOSHOT_PIPE)):
             if vname.startswith("oneshot") and S > (64 << 20) and world > 2:
                 continue
             if vname == "oneshot_push" and S * world > avg.capacity:
@@ -427,7 +433,7 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
                 avg.all_reduce_([[bufs[k[0] % len(bufs)]]], average=True, variant=v)
             med, best = timed(fused, iters)
             row["fused_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
-            if vname.endswith("_push"):
+            if vname.endswith("_push") or vname.endswith("_pipe"):
                 continue
             avg.bucket_acquire()
 
@@ -447,6 +453,56 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         del bufs
         avg.check_status()
         stage("sweep %d bytes: %s" % (S, {k2: round(v2["us"], 1) for k2, v2 in row.items() if isinstance(v2, dict)}))
+    return out
+
+
+def explore_pipe(avg, world, dev, dist):
+    """Tuning grid: pipelined two-shot push over (slots per block per round) x (block cap)."""
+    import torch
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import _lib
+    out = []
+    avg.reserve((256 << 20) + 4096)
+
+    def timed(fn, iters=30, warm=4):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(iters + 1)]
+        evs[0].record()
+        for i in range(iters):
+            fn()
+            evs[i + 1].record()
+        torch.cuda.synchronize()
+        t = torch.tensor([evs[i].elapsed_time(evs[i + 1]) for i in range(iters)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.sort().values[iters // 2]) * 1e3
+
+    for S in (16 << 20, 64 << 20, 256 << 20):
+        bufs = [torch.randn(S // 4, device=dev) for _ in range(3)]
+        k = [0]
+        row = {"bytes": S}
+        for vname, v in (("twoshot_push", ga.TWOSHOT_PUSH), ("twoshot", ga.TWOSHOT)):
+            def f():
+                k[0] += 1
+                avg.all_reduce_([[bufs[k[0] % 3]]], average=True, variant=v)
+            row[vname] = round(timed(f), 1)
+        for blocks in (0, 148, 74):
+            for group in (0, 1, 2, 4, 8, 16):
+                avg.set_option(_lib.OPT_MAX_BLOCKS, blocks)
+                avg.set_option(_lib.OPT_PIPE_GROUP, group)
+
+                def f():
+                    k[0] += 1
+                    avg.all_reduce_([[bufs[k[0] % 3]]], average=True, variant=ga.TWOSHOT_PIPE)
+                row["pipe_b%d_g%d" % (blocks, group)] = round(timed(f), 1)
+        avg.set_option(_lib.OPT_MAX_BLOCKS, 0)
+        avg.set_option(_lib.OPT_PIPE_GROUP, 0)
+        avg.check_status()
+        stage("explore %d: %s" % (S, row))
+        out.append(row)
+        del bufs
     return out
 
 

@@ -53,6 +53,8 @@ extern "C" {
 #define GA_VARIANT_ONESHOT_PUSH 3 /* every rank STORES its set into every peer's staging slot, local fold   */
 #define GA_VARIANT_TWOSHOT_PUSH 4 /* scatter to shard owners by remote stores, owner folds, result stored to
                                      every peer's gather region; pack folds into the scatter (tensor calls) */
+#define GA_VARIANT_TWOSHOT_PIPE 5 /* two-shot push, software-pipelined in rounds: scatter of round q+1 and
+                                     unpack of round q-1 overlap the fold of round q (large tensor calls)   */
 
 /* element type + operation */
 #define GA_OP_F32_AVG   0   /* fp32: rank-order sum, then / (float)world      mnist/main.py:126-127 */
@@ -63,6 +65,7 @@ extern "C" {
 #define GA_OPT_ONESHOT_MAX_BYTES 1   /* AUTO uses one-shot when bytes <= value */
 #define GA_OPT_TIMEOUT_MS        2   /* flag-wait timeout inside kernels; 0 = wait forever */
 #define GA_OPT_MAX_BLOCKS        3   /* cap on thread blocks per rank (0 = fill the device) */
+#define GA_OPT_PIPE_GROUP        4   /* TWOSHOT_PIPE: tile slots per block per round (0 = automatic) */
 
 typedef struct ga_ctx ga_ctx;
 

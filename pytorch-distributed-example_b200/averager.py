@@ -10,9 +10,9 @@ from . import _lib
 from ._lib import GradAvgError, check, load_library
 
 AUTO, ONESHOT, TWOSHOT = _lib.VARIANT_AUTO, _lib.VARIANT_ONESHOT, _lib.VARIANT_TWOSHOT
-ONESHOT_PUSH, TWOSHOT_PUSH = _lib.VARIANT_ONESHOT_PUSH, _lib.VARIANT_TWOSHOT_PUSH
+ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE = _lib.VARIANT_ONESHOT_PUSH, _lib.VARIANT_TWOSHOT_PUSH, _lib.VARIANT_TWOSHOT_PIPE
 _VARIANTS = {"auto": AUTO, "oneshot": ONESHOT, "1shot": ONESHOT, "twoshot": TWOSHOT, "2shot": TWOSHOT,
-             "oneshot_push": ONESHOT_PUSH, "twoshot_push": TWOSHOT_PUSH,
+             "oneshot_push": ONESHOT_PUSH, "twoshot_push": TWOSHOT_PUSH, "twoshot_pipe": TWOSHOT_PIPE, TWOSHOT_PIPE: TWOSHOT_PIPE,
              AUTO: AUTO, ONESHOT: ONESHOT, TWOSHOT: TWOSHOT, ONESHOT_PUSH: ONESHOT_PUSH, TWOSHOT_PUSH: TWOSHOT_PUSH,
              None: AUTO}
 

@@ -70,6 +70,8 @@ struct Params {
     uint32_t epoch;
     int rank_base;
     int direct;                 // 1: bucket-direct (no pack, result -> recv)
+    uint32_t rounds;            // pipelined two-shot push: rounds per launch (flags use epoch .. epoch+rounds-1)
+    uint32_t group;             //   and tile slots per block per round
     Seg inline_segs[kInlineSegs];
 };
 
@@ -565,6 +567,139 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     }
 }
 
+// Two-shot push, software-pipelined.  A block owns `group` tile slots per round; round q+1 is
+// scattered before round q is folded, and round q-1 is unpacked after round q's results were
+// pushed, so the links carry data while flags are in flight and while the local unpack runs:
+//
+//   scatter(0) | scatter(1) fold(0) | scatter(2) fold(1) unpack(0) | ... | unpack(R-1)
+//
+// Work inside a phase is spread over the 16 warps as (slot, destination) tiles for scatter and
+// unpack and as (slot, 512-byte row) items for the fold, whose W inputs must meet in one thread.
+template <int W, int OP>
+__global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_constant__ Params p) {
+    __shared__ int s_abort;
+    __shared__ int s_last;
+    const int ly = blockIdx.y;
+    const int r = p.rank_base + ly;
+    const int b = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t wpb = blockDim.x >> 5;
+    const uint32_t T = p.total_tiles, Ts = p.shard_tiles, G = p.group;
+    const int R = (int)p.rounds;
+    const float wf = (float)W;
+
+    Pad *mypad = p.pad[r];
+    const Vec *mystage = (const Vec *)p.send[r];
+    const Vec *mygather = (const Vec *)p.gather[r];
+    const Seg *segs = (p.dev_segs ? p.dev_segs : p.inline_segs) + (size_t)ly * p.n_seg;
+    const int n_seg = (int)p.n_seg;
+    const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
+    const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
+
+    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
+    __syncthreads();
+    if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+
+    auto slot0 = [&](int q) { return ((uint32_t)q * gridDim.x + b) * G; };
+
+    auto scatter = [&](int q) {
+        const uint32_t s0 = slot0(q);
+        for (uint32_t it = warp; it < G * W; it += wpb) {
+            const uint32_t i = s0 + it / W;
+            const int j = (r + (int)(it % W)) % W;
+            const uint32_t t = j * Ts + i;
+            if (i >= Ts || t >= T) continue;
+            const Seg sg = segs[find_seg(segs, n_seg, t)];
+            Vec v[kLaneVecs];
+            load_grad_tile(sg, t, lane, v);
+            Vec *dst = (Vec *)p.send[j] + ((size_t)r * Ts + i) * kTileVecs + lane;
+#pragma unroll
+            for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+        }
+    };
+
+    auto fold = [&](int q) {
+        const uint32_t s0 = slot0(q);
+        for (uint32_t it = warp; it < G * kLaneVecs; it += wpb) {
+            const uint32_t i = s0 + it / kLaneVecs;
+            const int u = (int)(it % kLaneVecs);
+            const uint32_t t = r * Ts + i;
+            if (i >= Ts || t >= T) continue;
+            const Seg sg = segs[find_seg(segs, n_seg, t)];
+            Vec v[W];
+#pragma unroll
+            for (int s = 0; s < W; ++s) v[s] = __ldcg(mystage + ((size_t)s * Ts + i) * kTileVecs + u * 32 + lane);
+            Vec acc[1] = {v[0]};
+#pragma unroll
+            for (int s = 1; s < W; ++s) {          // ((g0 + g1) + g2) + ...
+                acc[0].x = ElemOp<OP>::add(acc[0].x, v[s].x);
+                acc[0].y = ElemOp<OP>::add(acc[0].y, v[s].y);
+                acc[0].z = ElemOp<OP>::add(acc[0].z, v[s].z);
+                acc[0].w = ElemOp<OP>::add(acc[0].w, v[s].w);
+            }
+            acc[0].x = ElemOp<OP>::fin(acc[0].x, wf);
+            acc[0].y = ElemOp<OP>::fin(acc[0].y, wf);
+            acc[0].z = ElemOp<OP>::fin(acc[0].z, wf);
+            acc[0].w = ElemOp<OP>::fin(acc[0].w, wf);
+#pragma unroll
+            for (int jj = 1; jj < W; ++jj) {
+                const int j = (r + jj) % W;
+                __stcg((Vec *)p.gather[j] + (size_t)t * kTileVecs + u * 32 + lane, acc[0]);
+            }
+            store_grad_vecs<1>(sg, t, lane, u, acc);
+        }
+    };
+
+    auto unpack = [&](int q) {
+        if (W == 1) return;
+        const uint32_t s0 = slot0(q);
+        constexpr uint32_t kPeers = W > 1 ? W - 1 : 1;
+        for (uint32_t it = warp; it < G * kPeers; it += wpb) {
+            const uint32_t i = s0 + it / kPeers;
+            const int j = (r + 1 + (int)(it % kPeers)) % W;
+            const uint32_t t = j * Ts + i;
+            if (i >= Ts || t >= T) continue;
+            const Seg sg = segs[find_seg(segs, n_seg, t)];
+            const Vec *src = mygather + (size_t)t * kTileVecs + lane;
+            Vec v[kLaneVecs];
+#pragma unroll
+            for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcg(src + u * 32);
+            store_grad_vecs<kLaneVecs>(sg, t, lane, 0, v);
+        }
+    };
+
+    scatter(0);
+    raise_flags<W>(p, ready_off, p.epoch);
+    for (int q = 0; q < R; ++q) {
+        if (q + 1 < R) {
+            scatter(q + 1);
+            raise_flags<W>(p, ready_off, p.epoch + q + 1);
+        }
+        if (!wait_flags<W>(mypad->ready[b], p.epoch + q, p, &s_abort)) return;
+        fold(q);
+        raise_flags<W>(p, mid_off, p.epoch + q);
+        if (q > 0) {
+            if (!wait_flags<W>(mypad->mid[b], p.epoch + q - 1, p, &s_abort)) return;
+            unpack(q - 1);
+        }
+    }
+    if (!wait_flags<W>(mypad->mid[b], p.epoch + R - 1, p, &s_abort)) return;
+    unpack(R - 1);
+
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x == 0) mypad->finished_blocks = 0;
+        const size_t done_off = offsetof(Pad, done) / 4 + r;
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch + R - 1);
+    }
+}
+
 // Launched only when a bucket-direct call follows a tensor-list call: the caller is about to
 // overwrite the bucket from the host side of the stream, so every peer must have finished
 // reading it (tensor-list calls check this lazily, at the start of the NEXT kernel).
@@ -608,8 +743,14 @@ template <int W, int VARIANT> KernelFn pick_push_op(int op) {
            : op == GA_OP_F32_SUM ? (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_SUM>
                                  : (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_AVG>;
 }
+template <int W> KernelFn pick_pipe_op(int op) {
+    return op == GA_OP_I32_SUM   ? (KernelFn)ga_push_pipe_kernel<W, GA_OP_I32_SUM>
+           : op == GA_OP_F32_SUM ? (KernelFn)ga_push_pipe_kernel<W, GA_OP_F32_SUM>
+                                 : (KernelFn)ga_push_pipe_kernel<W, GA_OP_F32_AVG>;
+}
 template <int W> KernelFn pick_variant(int variant, int op) {
     switch (variant) {
+        case GA_VARIANT_TWOSHOT_PIPE: return pick_pipe_op<W>(op);
         case GA_VARIANT_TWOSHOT: return pick_op<W, GA_VARIANT_TWOSHOT>(op);
         case GA_VARIANT_ONESHOT_PUSH: return pick_push_op<W, GA_VARIANT_ONESHOT_PUSH>(op);
         case GA_VARIANT_TWOSHOT_PUSH: return pick_push_op<W, GA_VARIANT_TWOSHOT_PUSH>(op);
@@ -646,6 +787,7 @@ struct ga_ctx {
     uint32_t epoch;                 // epoch of the last launch
     int sm_count, blocks_per_sm[8];                  // by variant; 0 = not queried yet
     int max_blocks_opt;
+    int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
     size_t oneshot_max_bytes;
     unsigned long long timeout_ns;
     int *status_host, *status_dev;
@@ -754,11 +896,11 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     if (!c->opened) return fail(GA_ESTATE, "ga_open_peers has not been called");
     if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
     if (variant == GA_VARIANT_AUTO) variant = ga_pick_variant(c, (size_t)total_tiles * kTileBytes);
-    if (variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_TWOSHOT_PUSH) return fail(GA_EINVAL, "unknown variant %d", variant);
+    if (variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_TWOSHOT_PIPE) return fail(GA_EINVAL, "unknown variant %d", variant);
     if (total_tiles == 0) return GA_OK;    // nothing to average: no launch, epoch unchanged on every rank
     // Bucket-direct calls exist in the pull form only (their input already sits in the bucket).
     if (direct && variant == GA_VARIANT_ONESHOT_PUSH) variant = GA_VARIANT_ONESHOT;
-    if (direct && variant == GA_VARIANT_TWOSHOT_PUSH) variant = GA_VARIANT_TWOSHOT;
+    if (direct && (variant == GA_VARIANT_TWOSHOT_PUSH || variant == GA_VARIANT_TWOSHOT_PIPE)) variant = GA_VARIANT_TWOSHOT;
     // One-shot push stages W copies of the set in every rank's bucket; beyond that, two-shot push.
     if (variant == GA_VARIANT_ONESHOT_PUSH && (size_t)total_tiles * kTileBytes * c->world > c->capacity_bytes)
         variant = GA_VARIANT_TWOSHOT_PUSH;
@@ -803,7 +945,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
 
     KernelFn fn = pick_kernel(c->world, variant, op);
     // Grid: one warp per tile slot, at most what is co-resident (blocks spin on peers' flags).
-    const bool two_shot = variant == GA_VARIANT_TWOSHOT || variant == GA_VARIANT_TWOSHOT_PUSH;
+    const bool two_shot = variant == GA_VARIANT_TWOSHOT || variant == GA_VARIANT_TWOSHOT_PUSH || variant == GA_VARIANT_TWOSHOT_PIPE;
     const uint32_t slots = two_shot ? p.shard_tiles : total_tiles;
     const int wpb = kThreads / 32;
     int resident = blocks_per_sm(c, fn, variant) * c->sm_count / c->n_local;
@@ -811,6 +953,21 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     if (c->max_blocks_opt > 0 && resident > c->max_blocks_opt) resident = c->max_blocks_opt;
     if (resident < 1) resident = 1;
     int blocks = (int)((slots + wpb - 1) / wpb);
+    uint32_t rounds = 1;
+    if (variant == GA_VARIANT_TWOSHOT_PIPE) {
+        // `group` slots per block per round: about 8 rounds for large sets, never below 4 slots
+        // (so that the 16 warps of a block have work in every phase) nor above 16.
+        uint32_t group = c->pipe_group_opt ? (uint32_t)c->pipe_group_opt
+                                           : (slots + (uint32_t)resident * 8 - 1) / ((uint32_t)resident * 8);
+        if (!c->pipe_group_opt) { if (group < 4) group = 4; if (group > 16) group = 16; }
+        blocks = (int)((slots + group - 1) / group);
+        if (blocks > resident) blocks = resident;
+        if (blocks < 1) blocks = 1;
+        rounds = (slots + (uint32_t)blocks * group - 1) / ((uint32_t)blocks * group);
+        if (rounds < 1) rounds = 1;
+        p.group = group;
+    }
+    p.rounds = rounds;
     if (blocks > resident) blocks = resident;
     if (blocks < 1) blocks = 1;
 
@@ -822,7 +979,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     } else {
         CUDA_TRY(cudaLaunchKernel((const void *)fn, grid, block, args, 0, st));
     }
-    c->epoch += 1;
+    c->epoch += rounds;
     c->launches += 1;
     c->last_was_tensor_call = !direct;
     c->last_blocks = blocks;
@@ -1096,6 +1253,7 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
         case GA_OPT_ONESHOT_MAX_BYTES: c->oneshot_max_bytes = value < 0 ? 0 : (size_t)value; return GA_OK;
         case GA_OPT_TIMEOUT_MS: c->timeout_ns = value <= 0 ? 0 : (unsigned long long)value * 1000000ull; return GA_OK;
         case GA_OPT_MAX_BLOCKS: c->max_blocks_opt = value < 0 ? 0 : (int)value; return GA_OK;
+        case GA_OPT_PIPE_GROUP: c->pipe_group_opt = value < 0 ? 0 : (value > 64 ? 64 : (int)value); return GA_OK;
     }
     return fail(GA_EINVAL, "unknown option %d", option);
 }

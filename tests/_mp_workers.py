@@ -33,7 +33,7 @@ def ipc_world(rank, world, port, q, backend):
         # 1. the reference call on the MNIST set and the mini set, both variants
         for name, shapes in (("mini", oracle.MINI_SHAPES), ("mnist", oracle.MNIST_CNN_SHAPES)):
             host, want = fold(shapes)
-            for variant in ("oneshot", "twoshot", "oneshot_push", "twoshot_push"):
+            for variant in ("oneshot", "twoshot", "oneshot_push", "twoshot_push", "twoshot_pipe"):
                 params = [P(torch.from_numpy(a).cuda()) for a in host[rank]]
                 ga.average_gradients(params, variant=variant)
                 avg.check_status()
@@ -48,7 +48,7 @@ def ipc_world(rank, world, port, q, backend):
         keep = []
         for step in range(200):
             shapes = sets[step % len(sets)]
-            variant = ("oneshot", "twoshot_push", "twoshot", "oneshot_push")[(step // 3) % 4]
+            variant = ("oneshot", "twoshot_push", "twoshot", "oneshot_push", "twoshot_pipe")[(step // 3) % 5]
             slow = int(rng.integers(0, world))
             cycles = int(rng.integers(0, 3_000_000))
             if rank == slow:
