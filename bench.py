@@ -363,6 +363,9 @@ def main():
 
         if not args.no_extras and rank == 0 and not multi:
             line["extras"] = extras_single_gpu(avg, world, dev)
+        if not args.no_extras:
+            stage("mnist steps/sec leg")
+            line["mnist_steps_per_sec"] = mnist_leg(avg, world, hosted, dev, dist if multi else None, rank)
         if multi and args.sweep:
             line["sweep"] = sweep_multi(avg, world, dev, dist, args.sweep_max)
         if multi and args.explore:
@@ -453,6 +456,82 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         del bufs
         avg.check_status()
         stage("sweep %d bytes: %s" % (S, {k2: round(v2["us"], 1) for k2, v2 in row.items() if isinstance(v2, dict)}))
+    return out
+
+
+def mnist_leg(avg, world, hosted, dev, dist, rank, steps=200, batch=128):
+    """BASELINE metric, second half: synthetic-MNIST steps/sec with the reference's step order
+    (mnist/main.py:84-99: H2D of the batch, forward, zero_grad, backward, average, Adam step,
+    loss.item()).  `ours` = fused averaging; `per_tensor_nccl` (N > 1) = the reference's own
+    GPU path, one all_reduce + one div_ per parameter.  Hosted worlds run the `hosted` replicas
+    one after another on the one GPU.  steps/sec counts optimizer steps of the whole job per
+    second / world (i.e. synchronous data-parallel steps)."""
+    import torch
+    import torch.nn.functional as F
+    sys.path.insert(0, os.path.join(ROOT, "examples"))
+    import mnist_main
+
+    def run(mode):
+        nets, opts, data = [], [], []
+        for l in range(hosted):
+            torch.manual_seed(0)
+            net = mnist_main.Net().to(dev)
+            nets.append(net)
+            opts.append(torch.optim.Adam(net.parameters(), lr=1e-3))
+            data.append(mnist_main.SyntheticBatches(steps + 10, batch, rank + l))
+        iters = [iter(d) for d in data]
+
+        def one_step():
+            for l in range(hosted):
+                x, y = next(iters[l])
+                x, y = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+                loss = F.cross_entropy(nets[l](x), y)
+                opts[l].zero_grad()
+                loss.backward()
+                if hosted == 1:
+                    average(nets, mode)
+                    opts[l].step()
+                    loss.item()
+            if hosted > 1:
+                average(nets, mode)
+                for l in range(hosted):
+                    opts[l].step()
+                loss.item()
+
+        def average(nets, mode):
+            if mode == "ours":
+                if hosted == 1:
+                    avg.average_gradients(nets[0].parameters())
+                else:
+                    avg.average_gradients_local([n.parameters() for n in nets])
+            elif mode == "per_tensor_nccl":
+                for p in nets[0].parameters():                       # mnist/main.py:125-127 on NCCL
+                    dist.all_reduce(p.grad.data, op=dist.ReduceOp.SUM)
+                    p.grad.data /= float(world)
+
+        for _ in range(10):
+            one_step()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            one_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t)
+        return steps / dt
+
+    out = {"steps": steps, "batch_per_rank": batch, "world_size": world,
+           "what": "mnist/main.py:84-99 step order, synthetic 128x1x28x28 batches from pinned host memory, Adam lr 1e-3"}
+    out["ours"] = run("ours")
+    if dist is not None:
+        out["per_tensor_nccl"] = run("per_tensor_nccl")
+    else:
+        out["no_averaging_same_replicas"] = run("none")
     return out
 
 

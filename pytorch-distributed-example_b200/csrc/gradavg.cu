@@ -789,6 +789,7 @@ struct ga_ctx {
     int max_blocks_opt;
     int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
     size_t oneshot_max_bytes;
+    size_t pipe_min_bytes;          // AUTO: two-shot sets at least this large use the pipelined kernel
     unsigned long long timeout_ns;
     int *status_host, *status_dev;
     Seg *seg_host[kSegRing], *seg_dev[kSegRing];
@@ -828,7 +829,13 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->capacity_bytes = (capacity_bytes + kTileBytes - 1) / kTileBytes * kTileBytes;
     if (c->capacity_bytes / kTileBytes > 0xffffffffull) { free(c); return fail(GA_ECAPACITY, "capacity too large"); }
     c->region_bytes = c->capacity_bytes + (size_t)kMaxWorld * kTileBytes;
-    c->oneshot_max_bytes = world <= 2 ? (size_t)-1 : (size_t)512 << 10;
+    // AUTO thresholds, from the round-1 sweeps (profiles/): hosted worlds move everything through
+    // HBM and prefer the pull kernels; across GPUs the push kernels win at every size, one-shot
+    // while its (world-1)*S egress stays below ~8 MiB.
+    if (world <= 2) c->oneshot_max_bytes = (size_t)-1;
+    else if (n_local > 1) c->oneshot_max_bytes = (size_t)512 << 10;
+    else c->oneshot_max_bytes = ((size_t)8 << 20) / (size_t)(world - 1);
+    c->pipe_min_bytes = (size_t)8 << 20;
     c->timeout_ns = 30ull * 1000000000ull;
     c->host_chunk_bytes = (size_t)8 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
@@ -955,11 +962,12 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     int blocks = (int)((slots + wpb - 1) / wpb);
     uint32_t rounds = 1;
     if (variant == GA_VARIANT_TWOSHOT_PIPE) {
-        // `group` slots per block per round: about 8 rounds for large sets, never below 4 slots
-        // (so that the 16 warps of a block have work in every phase) nor above 16.
-        uint32_t group = c->pipe_group_opt ? (uint32_t)c->pipe_group_opt
-                                           : (slots + (uint32_t)resident * 8 - 1) / ((uint32_t)resident * 8);
-        if (!c->pipe_group_opt) { if (group < 4) group = 4; if (group > 16) group = 16; }
+        // Measured at 8 GPUs (profiles/r01b_explore_n8.md): 16 slots per block per round and one
+        // block per SM are best from 16 MiB to 256 MiB; smaller groups pay one flag round trip
+        // per round without moving enough bytes to hide it.
+        const uint32_t group = c->pipe_group_opt ? (uint32_t)c->pipe_group_opt : 16u;
+        if (c->max_blocks_opt == 0 && resident > c->sm_count / c->n_local) resident = c->sm_count / c->n_local;
+        if (resident < 1) resident = 1;
         blocks = (int)((slots + group - 1) / group);
         if (blocks > resident) blocks = resident;
         if (blocks < 1) blocks = 1;
@@ -1235,7 +1243,10 @@ size_t ga_capacity(const ga_ctx *c) { return c ? c->capacity_bytes : 0; }
 
 int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
     if (!c) return GA_VARIANT_ONESHOT;
-    return (c->world <= 2 || nbytes <= c->oneshot_max_bytes) ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
+    const bool one_shot = nbytes <= c->oneshot_max_bytes;
+    if (c->n_local > 1 || c->world == 1) return one_shot ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
+    if (one_shot && nbytes * c->world <= c->capacity_bytes) return GA_VARIANT_ONESHOT_PUSH;
+    return nbytes >= c->pipe_min_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
 }
 
 uint64_t ga_launch_count(const ga_ctx *c) { return c ? c->launches : 0; }
