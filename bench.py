@@ -178,7 +178,8 @@ def algorithmic_hbm_bytes(world, nbytes, variant_name, hosted):
                 "twoshot": 5.0 * s,                           # pack 2S, RS read S + write 2S/W, AG read+write (W-1)S/W each
                 "oneshot_push": (2 * w + 2) * s,              # read S, write W*S staging, read W*S, write S
                 "twoshot_push": (4.0 + 2.0 * (w - 1) / w) * s,  # read S, write S, read S, write S (grads+gather), unpack 2(W-1)S/W
-                "twoshot_pipe": (4.0 + 2.0 * (w - 1) / w) * s
+                "twoshot_pipe": (4.0 + 2.0 * (w - 1) / w) * s,
+                "hosted_direct": 2.0 * s                      # read every rank's gradient once, write every result once
                 }[variant_name]
     return per_rank * hosted
 
@@ -191,7 +192,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--bytes", type=int, default=DEFAULT_BYTES, help="gradient bytes per rank")
     ap.add_argument("--world", type=int, default=0, help="world size when --gpus 1 (default 4)")
-    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot", "oneshot_push", "twoshot_push", "twoshot_pipe"])
+    ap.add_argument("--variant", default="auto", choices=["auto", "oneshot", "twoshot", "oneshot_push", "twoshot_push", "twoshot_pipe", "hosted_direct"])
     ap.add_argument("--no-extras", action="store_true", help="skip the sweep / MNIST / cpu_baseline legs")
     ap.add_argument("--sweep", action="store_true", help="N > 1: size sweep 4 KB..1 GB, ours (both variants, fused and bucket) vs NCCL")
     ap.add_argument("--sweep-max", type=int, default=1 << 30)
@@ -229,10 +230,10 @@ def main():
     S = args.bytes - args.bytes % 4
     n = S // 4
     names = {ga.ONESHOT: "oneshot", ga.TWOSHOT: "twoshot", ga.ONESHOT_PUSH: "oneshot_push", ga.TWOSHOT_PUSH: "twoshot_push",
-             ga.TWOSHOT_PIPE: "twoshot_pipe"}
+             ga.TWOSHOT_PIPE: "twoshot_pipe", ga.HOSTED_DIRECT: "hosted_direct"}
     variant_id = {"auto": avg.pick_variant(S), "oneshot": ga.ONESHOT, "twoshot": ga.TWOSHOT,
                   "oneshot_push": ga.ONESHOT_PUSH, "twoshot_push": ga.TWOSHOT_PUSH,
-                  "twoshot_pipe": ga.TWOSHOT_PIPE}[args.variant]
+                  "twoshot_pipe": ga.TWOSHOT_PIPE, "hosted_direct": ga.HOSTED_DIRECT}[args.variant]
     variant_name = names[variant_id]
 
     # gradient sets: rotate so that consecutive steps never find their inputs in L2
@@ -624,11 +625,18 @@ def extras_single_gpu(avg, world, dev):
     for name, shapes in (("mnist_cnn_1.72MB_8_tensors", shapes_only.MNIST_CNN_SHAPES),
                          ("resnet18_46.76MB_62_tensors", shapes_only.resnet18_shapes())):
         out[name] = {"oneshot": time_set(shapes, ga.ONESHOT, 200), "twoshot": time_set(shapes, ga.TWOSHOT, 200)}
+    for name, shapes in list(out.items()):
+        out[name]["hosted_direct"] = time_set(shapes_only.MNIST_CNN_SHAPES if name.startswith("mnist") else
+                                              shapes_only.resnet18_shapes(), ga.HOSTED_DIRECT, 200)
     sweep = {}
-    for kb in (4, 64, 1024, 16384):
+    for kb in (4, 64, 1024, 16384, 65536):
         shp = [(kb * 256,)]
-        sweep["%dKB" % kb] = {"oneshot": time_set(shp, ga.ONESHOT, 200), "twoshot": time_set(shp, ga.TWOSHOT, 200)}
+        sweep["%dKB" % kb] = {"hosted_direct": time_set(shp, ga.HOSTED_DIRECT, 100),
+                              "oneshot": time_set(shp, ga.ONESHOT, 100), "twoshot": time_set(shp, ga.TWOSHOT, 100),
+                              "twoshot_push": time_set(shp, ga.TWOSHOT_PUSH, 100)}
     out["sweep_world%d_hosted" % world] = sweep
+    out["note"] = ("hosted_direct = no bucket (every rank's tensors addressed from one launch); oneshot/twoshot/"
+                   "twoshot_push = the cross-GPU protocol kernels run on the hosted world, same code as N > 1")
     return out
 
 

@@ -53,6 +53,8 @@ extern "C" {
 #define GA_VARIANT_ONESHOT_PUSH 3 /* every rank STORES its set into every peer's staging slot, local fold   */
 #define GA_VARIANT_TWOSHOT_PUSH 4 /* scatter to shard owners by remote stores, owner folds, result stored to
                                      every peer's gather region; pack folds into the scatter (tensor calls) */
+#define GA_VARIANT_HOSTED_DIRECT 6 /* ga_create_local only: every rank's tensors are addressable from one launch, so
+                                     each tile is read from all ranks, folded and written back: 2*W*S bytes, no bucket */
 #define GA_VARIANT_TWOSHOT_PIPE 5 /* two-shot push, software-pipelined in rounds: scatter of round q+1 and
                                      unpack of round q-1 overlap the fold of round q (large tensor calls)   */
 

@@ -17,9 +17,9 @@ from . import distributed  # noqa: F401
 from ._lib import GradAvgError, lib_path, load_library  # noqa: F401
 from .averager import (  # noqa: F401
     GradAverager, average_gradients, default_averager, reset_default_averager,
-    ONESHOT, TWOSHOT, AUTO, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE,
+    ONESHOT, TWOSHOT, AUTO, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT,
 )
 from .trainer import install  # noqa: F401
 
 __all__ = ["distributed", "GradAverager", "GradAvgError", "average_gradients", "default_averager",
-           "reset_default_averager", "install", "load_library", "lib_path", "ONESHOT", "TWOSHOT", "AUTO", "ONESHOT_PUSH", "TWOSHOT_PUSH", "TWOSHOT_PIPE"]
+           "reset_default_averager", "install", "load_library", "lib_path", "ONESHOT", "TWOSHOT", "AUTO", "ONESHOT_PUSH", "TWOSHOT_PUSH", "TWOSHOT_PIPE", "HOSTED_DIRECT"]

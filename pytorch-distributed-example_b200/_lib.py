@@ -8,6 +8,7 @@ _LIB = None
 GA_OK, GA_EINVAL, GA_ECUDA, GA_ECAPACITY, GA_ESTATE, GA_ETIMEOUT = 0, -1, -2, -3, -4, -5
 VARIANT_AUTO, VARIANT_ONESHOT, VARIANT_TWOSHOT = 0, 1, 2
 VARIANT_ONESHOT_PUSH, VARIANT_TWOSHOT_PUSH, VARIANT_TWOSHOT_PIPE = 3, 4, 5
+VARIANT_HOSTED_DIRECT = 6
 OP_F32_AVG, OP_I32_SUM, OP_F32_SUM = 0, 1, 2
 OPT_ONESHOT_MAX_BYTES, OPT_TIMEOUT_MS, OPT_MAX_BLOCKS, OPT_PIPE_GROUP = 1, 2, 3, 4
 IPC_HANDLE_BYTES = 64

@@ -11,8 +11,10 @@ from ._lib import GradAvgError, check, load_library
 
 AUTO, ONESHOT, TWOSHOT = _lib.VARIANT_AUTO, _lib.VARIANT_ONESHOT, _lib.VARIANT_TWOSHOT
 ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE = _lib.VARIANT_ONESHOT_PUSH, _lib.VARIANT_TWOSHOT_PUSH, _lib.VARIANT_TWOSHOT_PIPE
+HOSTED_DIRECT = _lib.VARIANT_HOSTED_DIRECT
 _VARIANTS = {"auto": AUTO, "oneshot": ONESHOT, "1shot": ONESHOT, "twoshot": TWOSHOT, "2shot": TWOSHOT,
              "oneshot_push": ONESHOT_PUSH, "twoshot_push": TWOSHOT_PUSH, "twoshot_pipe": TWOSHOT_PIPE, TWOSHOT_PIPE: TWOSHOT_PIPE,
+             "hosted_direct": _lib.VARIANT_HOSTED_DIRECT, _lib.VARIANT_HOSTED_DIRECT: _lib.VARIANT_HOSTED_DIRECT,
              AUTO: AUTO, ONESHOT: ONESHOT, TWOSHOT: TWOSHOT, ONESHOT_PUSH: ONESHOT_PUSH, TWOSHOT_PUSH: TWOSHOT_PUSH,
              None: AUTO}
 

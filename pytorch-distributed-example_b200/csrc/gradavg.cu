@@ -700,6 +700,66 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
     }
 }
 
+// Hosted world, no exchange at all: when every rank of the job lives in this process, their
+// gradient tensors are all addressable from one launch, so a tile is read once from each rank's
+// tensor, folded in rank order, divided and written back to every rank's tensor.  2*W*S bytes in
+// total, no bucket, no flags (each tile is complete in registers before anything is stored).
+__device__ __forceinline__ Vec load_grad_vec(const Seg &sg, uint32_t tile, int lane, int u) {
+    const uint32_t *src = (const uint32_t *)sg.ptr;
+    const size_t n = sg.numel;
+    const size_t e = (size_t)(tile - sg.start_tile) * kTileElems + (size_t)(u * 32 + lane) * 4;
+    Vec v;
+    if ((((uintptr_t)src) & 15) == 0 && e + 4 <= n) {
+        v = __ldcs((const Vec *)(src + e));
+    } else {
+        v.x = e + 0 < n ? __ldcs(src + e + 0) : 0u;
+        v.y = e + 1 < n ? __ldcs(src + e + 1) : 0u;
+        v.z = e + 2 < n ? __ldcs(src + e + 2) : 0u;
+        v.w = e + 3 < n ? __ldcs(src + e + 3) : 0u;
+    }
+    return v;
+}
+
+template <int W, int OP>
+__global__ void __launch_bounds__(kThreads, 2) ga_hosted_direct_kernel(const __grid_constant__ Params p) {
+    const Seg *segs = p.dev_segs ? p.dev_segs : p.inline_segs;      // [rank][n_seg], same layout for every rank
+    const int n_seg = (int)p.n_seg;
+    const int lane = threadIdx.x & 31;
+    const uint32_t wpb = blockDim.x >> 5;
+    const uint32_t stride = gridDim.x * wpb;
+    const float wf = (float)W;
+    constexpr int NU = W <= 4 ? 2 : 1;                               // vectors per rank in flight per thread
+    for (uint32_t t = blockIdx.x * wpb + (threadIdx.x >> 5); t < p.total_tiles; t += stride) {
+        const int si = find_seg(segs, n_seg, t);
+#pragma unroll
+        for (int u0 = 0; u0 < kLaneVecs; u0 += NU) {
+            Vec v[W][NU];
+#pragma unroll
+            for (int r = 0; r < W; ++r)
+#pragma unroll
+                for (int u = 0; u < NU; ++u) v[r][u] = load_grad_vec(segs[(size_t)r * n_seg + si], t, lane, u0 + u);
+            Vec acc[NU];
+#pragma unroll
+            for (int u = 0; u < NU; ++u) {
+                acc[u] = v[0][u];
+#pragma unroll
+                for (int r = 1; r < W; ++r) {      // ((g0 + g1) + g2) + ...
+                    acc[u].x = ElemOp<OP>::add(acc[u].x, v[r][u].x);
+                    acc[u].y = ElemOp<OP>::add(acc[u].y, v[r][u].y);
+                    acc[u].z = ElemOp<OP>::add(acc[u].z, v[r][u].z);
+                    acc[u].w = ElemOp<OP>::add(acc[u].w, v[r][u].w);
+                }
+                acc[u].x = ElemOp<OP>::fin(acc[u].x, wf);
+                acc[u].y = ElemOp<OP>::fin(acc[u].y, wf);
+                acc[u].z = ElemOp<OP>::fin(acc[u].z, wf);
+                acc[u].w = ElemOp<OP>::fin(acc[u].w, wf);
+            }
+#pragma unroll
+            for (int r = 0; r < W; ++r) store_grad_vecs<NU>(segs[(size_t)r * n_seg + si], t, lane, u0, acc);
+        }
+    }
+}
+
 // Launched only when a bucket-direct call follows a tensor-list call: the caller is about to
 // overwrite the bucket from the host side of the stream, so every peer must have finished
 // reading it (tensor-list calls check this lazily, at the start of the NEXT kernel).
@@ -748,8 +808,14 @@ template <int W> KernelFn pick_pipe_op(int op) {
            : op == GA_OP_F32_SUM ? (KernelFn)ga_push_pipe_kernel<W, GA_OP_F32_SUM>
                                  : (KernelFn)ga_push_pipe_kernel<W, GA_OP_F32_AVG>;
 }
+template <int W> KernelFn pick_hosted_op(int op) {
+    return op == GA_OP_I32_SUM   ? (KernelFn)ga_hosted_direct_kernel<W, GA_OP_I32_SUM>
+           : op == GA_OP_F32_SUM ? (KernelFn)ga_hosted_direct_kernel<W, GA_OP_F32_SUM>
+                                 : (KernelFn)ga_hosted_direct_kernel<W, GA_OP_F32_AVG>;
+}
 template <int W> KernelFn pick_variant(int variant, int op) {
     switch (variant) {
+        case GA_VARIANT_HOSTED_DIRECT: return pick_hosted_op<W>(op);
         case GA_VARIANT_TWOSHOT_PIPE: return pick_pipe_op<W>(op);
         case GA_VARIANT_TWOSHOT: return pick_op<W, GA_VARIANT_TWOSHOT>(op);
         case GA_VARIANT_ONESHOT_PUSH: return pick_push_op<W, GA_VARIANT_ONESHOT_PUSH>(op);
@@ -902,8 +968,16 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
     if (!c->opened) return fail(GA_ESTATE, "ga_open_peers has not been called");
     if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
-    if (variant == GA_VARIANT_AUTO) variant = ga_pick_variant(c, (size_t)total_tiles * kTileBytes);
-    if (variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_TWOSHOT_PIPE) return fail(GA_EINVAL, "unknown variant %d", variant);
+    if (variant == GA_VARIANT_AUTO) {
+        variant = ga_pick_variant(c, (size_t)total_tiles * kTileBytes);
+        if (direct && variant == GA_VARIANT_HOSTED_DIRECT)
+            variant = (size_t)total_tiles * kTileBytes <= c->oneshot_max_bytes ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
+    }
+    if (variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_HOSTED_DIRECT) return fail(GA_EINVAL, "unknown variant %d", variant);
+    if (variant == GA_VARIANT_HOSTED_DIRECT && c->n_local != c->world)
+        return fail(GA_EINVAL, "GA_VARIANT_HOSTED_DIRECT needs every rank hosted in this process (ga_create_local)");
+    if (variant == GA_VARIANT_HOSTED_DIRECT && direct)
+        variant = (size_t)total_tiles * kTileBytes <= c->oneshot_max_bytes ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     if (total_tiles == 0) return GA_OK;    // nothing to average: no launch, epoch unchanged on every rank
     // Bucket-direct calls exist in the pull form only (their input already sits in the bucket).
     if (direct && variant == GA_VARIANT_ONESHOT_PUSH) variant = GA_VARIANT_ONESHOT;
@@ -979,6 +1053,20 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     if (blocks > resident) blocks = resident;
     if (blocks < 1) blocks = 1;
 
+    if (variant == GA_VARIANT_HOSTED_DIRECT) {
+        // one launch over the tiles, every rank's tensors addressed directly: no flags, no epoch
+        int all = blocks_per_sm(c, fn, variant) * c->sm_count;
+        if (c->max_blocks_opt > 0 && all > c->max_blocks_opt) all = c->max_blocks_opt;
+        blocks = (int)((total_tiles + wpb - 1) / wpb);
+        if (blocks > all) blocks = all;
+        if (blocks < 1) blocks = 1;
+        void *hargs[] = {&p};
+        CUDA_TRY(cudaLaunchKernel((const void *)fn, dim3(blocks), dim3(kThreads), hargs, 0, st));
+        c->launches += 1;
+        c->last_blocks = blocks;
+        c->last_threads = kThreads;
+        return GA_OK;
+    }
     dim3 grid(blocks, c->n_local), block(kThreads);
     void *args[] = {&p};
     if (c->n_local > 1) {
@@ -1244,6 +1332,7 @@ size_t ga_capacity(const ga_ctx *c) { return c ? c->capacity_bytes : 0; }
 int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
     if (!c) return GA_VARIANT_ONESHOT;
     const bool one_shot = nbytes <= c->oneshot_max_bytes;
+    if (c->n_local > 1 && c->n_local == c->world) return GA_VARIANT_HOSTED_DIRECT;
     if (c->n_local > 1 || c->world == 1) return one_shot ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     if (one_shot && nbytes * c->world <= c->capacity_bytes) return GA_VARIANT_ONESHOT_PUSH;
     return nbytes >= c->pipe_min_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;

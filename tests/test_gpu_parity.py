@@ -17,8 +17,8 @@ import oracle
 
 pytestmark = pytest.mark.gpu
 
-ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE = 1, 2, 3, 4, 5
-ALL_VARIANTS = (ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE)
+ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT = 1, 2, 3, 4, 5, 6
+ALL_VARIANTS = (ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT)
 F32_AVG, I32_SUM, F32_SUM = 0, 1, 2
 
 
@@ -311,7 +311,7 @@ def test_repeated_steps_changing_pointers(lib):
         st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
         for step in range(300):
             shapes = sets[step % len(sets)]
-            variant = ALL_VARIANTS[(step // 2) % 5]
+            variant = ALL_VARIANTS[(step // 2) % 6]
             dev = [[torch.randn(s, device="cuda", generator=None) for s in shapes] for _ in range(world)]
             if step % 50 == 0:
                 expected.append((step, [[t.cpu().numpy().copy() for t in rank] for rank in dev]))

@@ -58,7 +58,7 @@ def _oracle_average(nets):
             p.grad.copy_(t)
 
 
-@pytest.mark.parametrize("world,variant", [(2, "oneshot"), (4, "twoshot"), (3, "twoshot_push"), (4, "oneshot_push")])
+@pytest.mark.parametrize("world,variant", [(2, "oneshot"), (4, "twoshot"), (3, "twoshot_push"), (4, "oneshot_push"), (4, "auto")])
 def test_loss_curve_matches_oracle_averaging(built, world, variant):
     import pytorch_distributed_example_b200 as ga
     torch.cuda.set_device(0)
