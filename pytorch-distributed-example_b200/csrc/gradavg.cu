@@ -1036,12 +1036,18 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     int blocks = (int)((slots + wpb - 1) / wpb);
     uint32_t rounds = 1;
     if (variant == GA_VARIANT_TWOSHOT_PIPE) {
-        // Measured at 8 GPUs (profiles/r01b_explore_n8.md): 16 slots per block per round and one
-        // block per SM are best from 16 MiB to 256 MiB; smaller groups pay one flag round trip
-        // per round without moving enough bytes to hide it.
-        const uint32_t group = c->pipe_group_opt ? (uint32_t)c->pipe_group_opt : 16u;
+        // Measured (profiles/r01b_explore_n8.md, r01e N=2): a round costs a flag round trip of a few
+        // tens of microseconds, so it must move >= ~32 MiB per GPU to hide it: one block per SM and
+        // `group` = 32 MiB / (world * 2 KiB * blocks) slots per block per round, at least 16.
         if (c->max_blocks_opt == 0 && resident > c->sm_count / c->n_local) resident = c->sm_count / c->n_local;
         if (resident < 1) resident = 1;
+        uint32_t group = (uint32_t)c->pipe_group_opt;
+        if (group == 0) {
+            const size_t per_slot = (size_t)c->world * kTileBytes * (size_t)resident;
+            group = (uint32_t)((((size_t)32 << 20) + per_slot - 1) / per_slot);
+            if (group < 16) group = 16;
+            if (group > 64) group = 64;
+        }
         blocks = (int)((slots + group - 1) / group);
         if (blocks > resident) blocks = resident;
         if (blocks < 1) blocks = 1;
