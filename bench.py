@@ -269,12 +269,12 @@ def main():
     barrier()
     stage("warm-up done, grid=%s" % (avg.last_grid,))
     launches0 = avg.launch_count
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
     w0 = time.time()
     ev[0].record()
     for i in range(args.steps):
         step(i)
-        ev[i + 1].record()
+    ev[1].record()
     torch.cuda.synchronize()
     if multi:
         dist.barrier()
@@ -282,10 +282,9 @@ def main():
     gpu_launches = avg.launch_count - launches0
     avg.check_status()
     stage("timed region done")
-    total_ms = max_over_ranks(ev[0].elapsed_time(ev[-1]))
-    per_launch_ms = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
-    kernel_ms = max_over_ranks(sum(per_launch_ms) / len(per_launch_ms))
+    total_ms = max_over_ranks(ev[0].elapsed_time(ev[1]))
     ms_per_step = total_ms / args.steps
+    kernel_ms = ms_per_step          # one launch per step: average launch duration incl. the launch gap
     value = agg_bus_gbps(world, S, ms_per_step / 1e3)
     grid = avg.last_grid
 

@@ -31,7 +31,7 @@ def main():
                 d[k] = {"value": r[i], "unit": units[i]}
         out.append(d)
     json.dump(out, open(prefix + "_metrics.json", "w"), indent=1)
-    fused = [d for d in out if "ga_fused_kernel" in d["kernel"]]
+    fused = [d for d in out if "::ga_" in d["kernel"] and "drain" not in d["kernel"]]
     if fused:
         def b(d, k):
             return float(d[k]["value"].replace(",", "")) * SCALE.get(d[k]["unit"], 1)
