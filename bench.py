@@ -368,6 +368,9 @@ def main():
         if not args.no_extras:
             stage("mnist steps/sec leg")
             line["mnist_steps_per_sec"] = mnist_leg(avg, world, hosted, dev, dist if multi else None, rank)
+        if multi and not args.no_extras:
+            stage("overlap leg")
+            line["resnet18_overlap"] = overlap_leg(avg, world, dev, dist)
         if multi and args.sweep:
             line["sweep"] = sweep_multi(avg, world, dev, dist, args.sweep_max)
         if multi and args.explore:
@@ -534,6 +537,65 @@ def mnist_leg(avg, world, hosted, dev, dist, rank, steps=200, batch=128):
         out["per_tensor_nccl"] = run("per_tensor_nccl")
     else:
         out["no_averaging_same_replicas"] = run("none")
+    return out
+
+
+def overlap_leg(avg, world, dev, dist, steps=30, batch=32):
+    """BASELINE configs[4]: ResNet-18 (62 gradient tensors, 46.76 MB) forward + backward on
+    randn(32,3,224,224); per-step averaging (a) absent, (b) one fused call after backward (the
+    reference's call site), (c) bucketed and overlapped with backward from grad hooks.  Exposed
+    averaging time = step time minus (a).  Device-timed, max over ranks."""
+    import torch
+    import torch.nn.functional as F
+    import pytorch_distributed_example_b200 as ga
+    try:
+        import torchvision
+        net = torchvision.models.resnet18(weights=None)
+    except Exception as e:                                     # torchvision missing: report, do not fake
+        return {"unavailable": "torchvision resnet18 not importable: %s" % e}
+    torch.manual_seed(0)
+    net = net.to(dev).to(memory_format=torch.channels_last)
+    x = torch.randn(batch, 3, 224, 224, device=dev).contiguous(memory_format=torch.channels_last)
+    y = torch.randint(0, 1000, (batch,), device=dev)
+    params = [p for p in net.parameters()]
+    ov = [None]
+
+    def step(mode):
+        for p in params:
+            p.grad = None
+        loss = F.cross_entropy(net(x), y)
+        loss.backward()
+        if mode == "after":
+            avg.average_gradients(params)
+        elif mode == "overlap":
+            ov[0].average_gradients()
+
+    def timed(mode):
+        for _ in range(5):
+            step(mode)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            step(mode)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+
+    out = {"model": "torchvision resnet18, batch %d, fp32, channels_last" % batch,
+           "grad_bytes": sum(p.numel() for p in params) * 4, "tensors": len(params)}
+    out["ms_no_averaging"] = timed("none")
+    out["ms_fused_after_backward"] = timed("after")
+    ov[0] = ga.OverlappedAverager(net, averager=avg, bucket_cap_bytes=16 << 20, max_blocks=32)
+    out["buckets"] = len(ov[0].buckets)
+    out["ms_overlapped"] = timed("overlap")
+    ov[0].remove()
+    out["exposed_us_after_backward"] = (out["ms_fused_after_backward"] - out["ms_no_averaging"]) * 1e3
+    out["exposed_us_overlapped"] = (out["ms_overlapped"] - out["ms_no_averaging"]) * 1e3
+    avg.check_status()
     return out
 
 

@@ -20,6 +20,7 @@ from .averager import (  # noqa: F401
     ONESHOT, TWOSHOT, AUTO, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT,
 )
 from .trainer import install  # noqa: F401
+from .overlap import OverlappedAverager, plan_buckets  # noqa: F401
 
 __all__ = ["distributed", "GradAverager", "GradAvgError", "average_gradients", "default_averager",
-           "reset_default_averager", "install", "load_library", "lib_path", "ONESHOT", "TWOSHOT", "AUTO", "ONESHOT_PUSH", "TWOSHOT_PUSH", "TWOSHOT_PIPE", "HOSTED_DIRECT"]
+           "reset_default_averager", "install", "OverlappedAverager", "plan_buckets", "load_library", "lib_path", "ONESHOT", "TWOSHOT", "AUTO", "ONESHOT_PUSH", "TWOSHOT_PUSH", "TWOSHOT_PIPE", "HOSTED_DIRECT"]

@@ -97,6 +97,45 @@ def ipc_world(rank, world, port, q, backend):
             torch.cuda.synchronize()
             if pinned.numpy().tobytes() != want.tobytes():
                 out["fail"].append("host form " + variant)
+        # 5. overlapped, bucketed averaging from grad hooks == the single call after backward
+        from pytorch_distributed_example_b200 import workloads
+        shapes5 = workloads.resnet18_shapes()[-20:]
+
+        class Bag(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.ps = torch.nn.ParameterList([torch.nn.Parameter(torch.zeros(s)) for s in shapes5])
+
+            def forward(self, x):
+                acc = x
+                for p in self.ps:
+                    acc = torch.tanh(acc + p.reshape(-1)[:4].sum() * x)
+                return acc.sum()
+
+        nets = []
+        for mode in ("overlap", "after"):
+            torch.manual_seed(1)
+            net = Bag().cuda()
+            with torch.no_grad():
+                for p in net.parameters():
+                    p.normal_()
+            x = torch.randn(64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(9 + rank))
+            ov = ga.OverlappedAverager(net, averager=avg, bucket_cap_bytes=4 << 20, max_blocks=16) if mode == "overlap" else None
+            for step in range(3):
+                net.zero_grad()
+                net(x * (step + 1)).backward()
+                if ov is not None:
+                    ov.average_gradients()
+                else:
+                    avg.average_gradients(net.parameters())
+            if ov is not None:
+                ov.remove()
+            avg.check_status()
+            nets.append(net)
+        for pa, pb in zip(nets[0].parameters(), nets[1].parameters()):
+            if pa.grad.cpu().numpy().tobytes() != pb.grad.cpu().numpy().tobytes():
+                out["fail"].append("overlap != after-backward")
+                break
         out["launches"] = avg.launch_count
         tdist.barrier()
         ga.reset_default_averager()

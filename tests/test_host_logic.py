@@ -104,3 +104,16 @@ def test_workload_shapes_agree_with_oracle_tables():
     from pytorch_distributed_example_b200 import workloads
     assert workloads.MNIST_CNN_SHAPES == oracle.MNIST_CNN_SHAPES
     assert workloads.resnet18_shapes() == oracle.resnet18_shapes()
+
+
+def test_bucket_plan_reverse_order_and_cap():
+    from pytorch_distributed_example_b200 import plan_buckets, workloads
+    numels = [workloads.numel(s) for s in workloads.resnet18_shapes()]
+    buckets = plan_buckets(numels, 25 << 20)
+    flat = [i for b in buckets for i in b]
+    assert flat == list(reversed(range(len(numels))))                  # last parameter first, nothing lost
+    for b in buckets:
+        assert averager.bucket_bytes([numels[i] for i in b]) <= (25 << 20) or len(b) == 1
+    assert len(buckets) >= 2
+    assert plan_buckets([10, 10], 1) == [[1], [0]]                      # a bucket always takes one tensor
+    assert plan_buckets([], 1 << 20) == []
