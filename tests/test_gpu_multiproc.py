@@ -46,3 +46,41 @@ def test_four_ranks_ipc():
 @pytest.mark.skipif(torch.cuda.device_count() < 8, reason="needs 8 GPUs")
 def test_eight_ranks_ipc():
     _run(8, "nccl")
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_reference_style_script_two_ranks(tmp_path):
+    """A script in the reference's style, run by the drop-in runner on 2 GPUs: once with the fused
+    `average_gradients` installed, once with its own per-tensor loop over our `distributed.all_reduce`.
+    At world_size 2 `/ 2.0` is exact either way, so both runs print the same final losses."""
+    import os
+    import subprocess
+    import sys
+    from oracle.gloo_path import free_port
+    from tests.test_run_script import STYLE_SCRIPT, ROOT
+    script = tmp_path / "main.py"
+    script.write_text(STYLE_SCRIPT)
+    losses = {}
+    for mode in ("fused", "per-tensor"):
+        port = free_port()
+        procs = []
+        for r in range(2):
+            cmd = [sys.executable, "-m", "pytorch_distributed_example_b200.run_script", str(script), "--ga-synthetic", "6"]
+            if mode == "per-tensor":
+                cmd.append("--ga-per-tensor")
+            cmd += ["--", "--rank", str(r), "--world-size", "2", "--backend", "gloo", "-i", "tcp://127.0.0.1:%d" % port]
+            env = dict(os.environ, GA_TIMEOUT_MS="8000")
+            procs.append(subprocess.Popen(cmd, cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env))
+        outs = []
+        for p in procs:
+            try:
+                o, e = p.communicate(timeout=240)
+            except subprocess.TimeoutExpired:
+                for q in procs:
+                    q.kill()
+                raise
+            assert p.returncode == 0, e[-2000:]
+            outs.append(o)
+        losses[mode] = [[l for l in o.splitlines() if l.startswith("final loss")][0] for o in outs]
+        assert all("done" in o for o in outs)
+    assert losses["fused"] == losses["per-tensor"]
