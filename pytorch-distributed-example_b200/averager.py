@@ -60,7 +60,9 @@ class GradAverager:
         if not 1 <= self.world_size <= _lib.MAX_WORLD:
             raise GradAvgError(_lib.GA_EINVAL, "world_size %d outside 1..%d" % (self.world_size, _lib.MAX_WORLD))
         self._device = device
+        self._dev_obj = None
         self._ptr_cache = {}
+        self._plans = {}
         if capacity_bytes:
             self._create(capacity_bytes)
 
@@ -71,10 +73,14 @@ class GradAverager:
 
     @property
     def device(self):
-        if self._device is None:
-            _require_cuda()
-            self._device = torch.cuda.current_device()
-        return torch.device("cuda", self._device) if isinstance(self._device, int) else torch.device(self._device)
+        d = self._dev_obj
+        if d is None:
+            if self._device is None:
+                _require_cuda()
+                self._device = torch.cuda.current_device()
+            d = torch.device("cuda", self._device) if isinstance(self._device, int) else torch.device(self._device)
+            self._dev_obj = d
+        return d
 
     def _create(self, capacity_bytes):
         _require_cuda()
@@ -187,17 +193,61 @@ class GradAverager:
             v = self._variant if variant is None else _VARIANTS[variant]
             check(self._lib.ga_allreduce_tensors(self._ctx, ptrs, numel, n, op, ctypes.c_void_p(stream), v))
 
+    def _run_params(self, per_rank_params, variant):
+        """Hot path of the training loop.  The element counts of a parameter list never change, so
+        they are laid out once per list (keyed by the identity of its parameters); every call then
+        only re-reads the gradient pointers and checks dtype / device / contiguity."""
+        flat = [p for ps in per_rank_params for p in ps]
+        key = tuple(map(id, flat))
+        plan = self._plans.get(key)
+        if plan is None:
+            if len(self._plans) > 16:
+                self._plans.clear()
+            n = len(per_rank_params[0])
+            if any(len(ps) != n for ps in per_rank_params):
+                raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different parameter counts")
+            numels = [p.numel() for p in per_rank_params[0]]
+            for ps in per_rank_params[1:]:
+                if [p.numel() for p in ps] != numels:
+                    raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different parameter sizes")
+            plan = (n, (ctypes.c_void_p * len(flat))(), (ctypes.c_int64 * n)(*numels), bucket_bytes(numels))
+            self._plans[key] = plan
+        n, ptrs, numel, need = plan
+        with self._lock:
+            self._ensure(need)
+            dev_index = self.device.index
+            f32 = torch.float32
+            k = 0
+            for p in flat:
+                g = p.grad
+                if g is None:
+                    # the reference would raise AttributeError on `None.data` (mnist/main.py:126)
+                    raise AttributeError("parameter without .grad: 'NoneType' object has no attribute 'data'")
+                if g.dtype is not f32 or g.get_device() != dev_index or not g.is_contiguous():
+                    raise GradAvgError(_lib.GA_EINVAL, "gradient %d: need contiguous float32 on cuda:%s, got %s on %s "
+                                       "(no CPU fallback)" % (k % n, dev_index, g.dtype, g.device))
+                ptrs[k] = g.data_ptr()
+                k += 1
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            v = self._variant if variant is None else _VARIANTS[variant]
+            check(self._lib.ga_average(self._ctx, ptrs, numel, n, ctypes.c_void_p(stream), v))
+
     def average_gradients(self, params, variant=None):
         """`Trainer.average_gradients` (mnist/main.py:122-127) for one rank: every `p.grad` is
         replaced IN PLACE by the rank-order sum over all ranks divided by float(world_size).
         Stream-ordered on torch's current stream; returns after the launch."""
-        self._run_tensors([self._grads_of(params)], _lib.OP_F32_AVG, torch.float32, variant)
+        if isinstance(params, torch.nn.Module):
+            params = params.parameters()
+        if self.n_local != 1:
+            raise GradAvgError(_lib.GA_EINVAL, "this averager hosts %d ranks: use average_gradients_local" % self.n_local)
+        self._run_params([list(params)], variant)
 
     def average_gradients_local(self, per_rank_params, variant=None):
         """Same for a local world: one parameter list per hosted rank, rank order."""
         if len(per_rank_params) != self.n_local:
             raise GradAvgError(_lib.GA_EINVAL, "need %d parameter lists" % self.n_local)
-        self._run_tensors([self._grads_of(p) for p in per_rank_params], _lib.OP_F32_AVG, torch.float32, variant)
+        self._run_params([list(ps.parameters() if isinstance(ps, torch.nn.Module) else ps) for ps in per_rank_params],
+                         variant)
 
     def all_reduce_(self, tensors, average=False, variant=None):
         """In-place SUM (or average) of a list of CUDA tensors (fp32 or int32), one list per hosted
