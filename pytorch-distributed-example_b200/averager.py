@@ -28,6 +28,20 @@ def bucket_bytes(numels):
     return sum(_tiles(n) for n in numels) * _lib.TILE_BYTES
 
 
+def _dense(t):
+    """True if the tensor's storage is one dense run of numel elements (default, channels_last or
+    channels_last_3d layout).  The average is elementwise, so any such layout can be treated as a
+    flat array as long as every rank uses the same one -- which data-parallel replicas do."""
+    if t.is_contiguous():
+        return True
+    d = t.dim()
+    if d == 4:
+        return t.is_contiguous(memory_format=torch.channels_last)
+    if d == 5:
+        return t.is_contiguous(memory_format=torch.channels_last_3d)
+    return False
+
+
 def _require_cuda():
     if not torch.cuda.is_available():
         raise GradAvgError(_lib.GA_ESTATE, "no CUDA device: this path has no CPU fallback")
@@ -173,8 +187,8 @@ class GradAverager:
                 if t.dtype != dtype or not t.is_cuda or t.device != dev:
                     raise GradAvgError(_lib.GA_EINVAL, "tensor %d: need %s on %s, got %s on %s (no CPU fallback)"
                                        % (i, dtype, dev, t.dtype, t.device))
-                if not t.is_contiguous():
-                    raise GradAvgError(_lib.GA_EINVAL, "tensor %d is not contiguous" % i)
+                if not _dense(t):
+                    raise GradAvgError(_lib.GA_EINVAL, "tensor %d is not dense (strides %s)" % (i, tuple(t.stride())))
                 ptrs[k] = t.data_ptr()
                 k += 1
         for i, t in enumerate(per_rank_tensors[0]):
@@ -206,9 +220,13 @@ class GradAverager:
             n = len(per_rank_params[0])
             if any(len(ps) != n for ps in per_rank_params):
                 raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different parameter counts")
-            numels = [p.numel() for p in per_rank_params[0]]
+            def _n(p):
+                if p.grad is None:      # the reference would raise AttributeError on `None.data` (mnist/main.py:126)
+                    raise AttributeError("parameter without .grad: 'NoneType' object has no attribute 'data'")
+                return p.grad.numel()
+            numels = [_n(p) for p in per_rank_params[0]]
             for ps in per_rank_params[1:]:
-                if [p.numel() for p in ps] != numels:
+                if [_n(p) for p in ps] != numels:
                     raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different parameter sizes")
             plan = (n, (ctypes.c_void_p * len(flat))(), (ctypes.c_int64 * n)(*numels), bucket_bytes(numels))
             self._plans[key] = plan
@@ -223,9 +241,9 @@ class GradAverager:
                 if g is None:
                     # the reference would raise AttributeError on `None.data` (mnist/main.py:126)
                     raise AttributeError("parameter without .grad: 'NoneType' object has no attribute 'data'")
-                if g.dtype is not f32 or g.get_device() != dev_index or not g.is_contiguous():
-                    raise GradAvgError(_lib.GA_EINVAL, "gradient %d: need contiguous float32 on cuda:%s, got %s on %s "
-                                       "(no CPU fallback)" % (k % n, dev_index, g.dtype, g.device))
+                if g.dtype is not f32 or g.get_device() != dev_index or not _dense(g):
+                    raise GradAvgError(_lib.GA_EINVAL, "gradient %d: need dense float32 on cuda:%s, got %s on %s, strides %s "
+                                       "(no CPU fallback)" % (k % n, dev_index, g.dtype, g.device, tuple(g.stride())))
                 ptrs[k] = g.data_ptr()
                 k += 1
             stream = torch.cuda.current_stream(self.device).cuda_stream

@@ -406,3 +406,39 @@ def test_resnet18_set(lib):
             _assert_all_ranks_equal(dev, want, "resnet18 v=%d" % variant)
     finally:
         w.close()
+
+
+def test_python_layer_layouts_and_errors(built):
+    """GradAverager: channels_last gradients are accepted (dense, elementwise op), strided views
+    and wrong dtypes / devices are rejected loudly, a parameter without .grad raises AttributeError."""
+    import pytorch_distributed_example_b200 as ga
+    torch.cuda.set_device(0)
+    world = 2
+    avg = ga.GradAverager(local_world=world, device=0)
+    try:
+        ps = []
+        for r in range(world):
+            p = torch.nn.Parameter(torch.zeros(8, 4, 3, 3, device="cuda").to(memory_format=torch.channels_last))
+            p.grad = torch.randn(8, 4, 3, 3, device="cuda", generator=torch.Generator(device="cuda").manual_seed(r)) \
+                .to(memory_format=torch.channels_last)
+            ps.append([p])
+        want = (ps[0][0].grad + ps[1][0].grad) / 2.0
+        avg.average_gradients_local(ps)
+        assert torch.equal(ps[0][0].grad, want) and torch.equal(ps[1][0].grad, want)
+        assert ps[0][0].grad.is_contiguous(memory_format=torch.channels_last)
+        bad = torch.nn.Parameter(torch.zeros(16, device="cuda"))
+        bad.grad = torch.zeros(32, device="cuda")[::2]
+        with pytest.raises(ga.GradAvgError):
+            avg.average_gradients_local([[bad], [bad]])
+        half = torch.nn.Parameter(torch.zeros(4, device="cuda"))
+        half.grad = torch.zeros(4, device="cuda")
+        half.grad.data = half.grad.data  # no-op; dtype check below
+        dbl = torch.nn.Parameter(torch.zeros(4, device="cuda", dtype=torch.float64))
+        dbl.grad = torch.zeros(4, device="cuda", dtype=torch.float64)
+        with pytest.raises(ga.GradAvgError):
+            avg.average_gradients_local([[dbl], [dbl]])
+        nog = torch.nn.Parameter(torch.zeros(4, device="cuda"))
+        with pytest.raises(AttributeError):
+            avg.average_gradients_local([[nog], [nog]])
+    finally:
+        avg.close()
