@@ -64,6 +64,7 @@ class OverlappedAverager:
             for i in idx:
                 self._bucket_of[i] = k
         self._need = [len(idx) * len(self.modules) for idx in self.buckets]
+        self._bucket_params = [[[ps[i] for i in idx] for ps in self.params] for idx in self.buckets]
         self._lock = threading.Lock()
         self._side = None
         self._handles = []
@@ -99,18 +100,16 @@ class OverlappedAverager:
         ready = torch.cuda.Event()
         ready.record(cur)                    # gradients of this bucket are final at this point of backward
         self._side.wait_event(ready)
-        idx = self.buckets[k]
-        lists = [[ps[i].grad.data for i in idx] for ps in self.params]
+        # The gradients stay alive until the next zero_grad(), which comes after average_gradients()
+        # has made the current stream wait for this kernel, so no record_stream is needed.
         with torch.cuda.stream(self._side):
             if self.max_blocks:
                 self.avg.set_option(_lib.OPT_MAX_BLOCKS, self.max_blocks)
             try:
-                self.avg.all_reduce_(lists, average=True, variant=self.variant)
+                self.avg._run_params(self._bucket_params[k], self.variant)
             finally:
                 if self.max_blocks:
                     self.avg.set_option(_lib.OPT_MAX_BLOCKS, 0)
-        for g in (t for l in lists for t in l):
-            g.record_stream(self._side)      # the caching allocator must not recycle them under the kernel
         self._launched += 1
 
     def average_gradients(self):

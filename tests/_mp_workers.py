@@ -16,6 +16,11 @@ def ipc_world(rank, world, port, q, backend):
     from pytorch_distributed_example_b200 import distributed as dist, _lib
 
     out = {"rank": rank, "fail": []}
+    import time as _time
+    _t0 = _time.time()
+
+    def note(msg):
+        print("[ipc_world rank %d %5.1fs] %s" % (rank, _time.time() - _t0, msg), file=sys.stderr, flush=True)
     try:
         os.environ.setdefault("GA_TIMEOUT_MS", "8000")
         dist.init_process_group(backend=backend, init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
@@ -30,6 +35,7 @@ def ipc_world(rank, world, port, q, backend):
             def __init__(self, g):
                 self.grad = g
 
+        note("group up, averager ready")
         # 1. the reference call on the MNIST set and the mini set, both variants
         for name, shapes in (("mini", oracle.MINI_SHAPES), ("mnist", oracle.MNIST_CNN_SHAPES)):
             host, want = fold(shapes)
@@ -41,6 +47,7 @@ def ipc_world(rank, world, port, q, backend):
                     if p.grad.cpu().numpy().tobytes() != w.tobytes():
                         out["fail"].append("%s %s tensor %d" % (name, variant, i))
 
+        note("part 1 done")
         # 2. skew stress: random extra GPU work before the call on a random rank, fresh pointers,
         #    alternating sizes and variants, no host sync between steps
         rng = np.random.default_rng(42)                       # same stream on every rank
@@ -74,6 +81,7 @@ def ipc_world(rank, world, port, q, backend):
                 if p.grad.cpu().numpy().tobytes() != want.tobytes():
                     out["fail"].append("skew step %d tensor %d" % (step, i))
 
+        note("part 2 done")
         # 3. toy path: int32 SUM of a host IntTensor through distributed.all_reduce (toy/main.py:15-20)
         group = dist.new_group(ranks=list(range(world)))
         t = torch.IntTensor([rank + 3])
@@ -81,6 +89,7 @@ def ipc_world(rank, world, port, q, backend):
         if int(t) != sum(r + 3 for r in range(world)):
             out["fail"].append("toy int32 sum %d" % int(t))
 
+        note("part 3 done")
         # 4. bucket-direct and host forms
         n = 262144 + 3
         host = [np.random.default_rng(r).standard_normal(n).astype(np.float32) for r in range(world)]
@@ -97,6 +106,7 @@ def ipc_world(rank, world, port, q, backend):
             torch.cuda.synchronize()
             if pinned.numpy().tobytes() != want.tobytes():
                 out["fail"].append("host form " + variant)
+        note("part 4 done")
         # 5. overlapped, bucketed averaging from grad hooks == the single call after backward
         from pytorch_distributed_example_b200 import workloads
         shapes5 = workloads.resnet18_shapes()[-20:]
@@ -121,6 +131,7 @@ def ipc_world(rank, world, port, q, backend):
                     p.normal_()
             x = torch.randn(64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(9 + rank))
             ov = ga.OverlappedAverager(net, averager=avg, bucket_cap_bytes=4 << 20, max_blocks=16) if mode == "overlap" else None
+            note("part 5 %s: averager built" % mode)
             for step in range(3):
                 net.zero_grad()
                 net(x * (step + 1)).backward()
@@ -130,7 +141,9 @@ def ipc_world(rank, world, port, q, backend):
                     avg.average_gradients(net.parameters())
             if ov is not None:
                 ov.remove()
+            note("part 5 %s: steps enqueued" % mode)
             avg.check_status()
+            note("part 5 %s: done" % mode)
             nets.append(net)
         for pa, pb in zip(nets[0].parameters(), nets[1].parameters()):
             if pa.grad.cpu().numpy().tobytes() != pb.grad.cpu().numpy().tobytes():

@@ -19,7 +19,7 @@ def _run(world, backend):
     res = []
     try:
         for _ in procs:
-            res.append(q.get(timeout=240))
+            res.append(q.get(timeout=150))
             if res[-1]["fail"]:
                 break                                   # one rank failed: the others may be stuck in a collective
     finally:
