@@ -228,9 +228,10 @@ class GradAverager:
             for ps in per_rank_params[1:]:
                 if [_n(p) for p in ps] != numels:
                     raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different parameter sizes")
-            plan = (n, (ctypes.c_void_p * len(flat))(), (ctypes.c_int64 * n)(*numels), bucket_bytes(numels))
+            # `flat` is kept in the plan: while the parameters are alive their ids cannot be reused
+            plan = (n, (ctypes.c_void_p * len(flat))(), (ctypes.c_int64 * n)(*numels), bucket_bytes(numels), flat, numels)
             self._plans[key] = plan
-        n, ptrs, numel, need = plan
+        n, ptrs, numel, need, _keepalive, numels = plan
         with self._lock:
             self._ensure(need)
             dev_index = self.device.index
@@ -241,6 +242,10 @@ class GradAverager:
                 if g is None:
                     # the reference would raise AttributeError on `None.data` (mnist/main.py:126)
                     raise AttributeError("parameter without .grad: 'NoneType' object has no attribute 'data'")
+                if g.numel() != numels[k % n]:
+                    del self._plans[key]
+                    raise GradAvgError(_lib.GA_EINVAL, "gradient %d changed size since the first call with this "
+                                       "parameter list (%d -> %d elements)" % (k % n, numels[k % n], g.numel()))
                 if g.dtype is not f32 or g.get_device() != dev_index or not _dense(g):
                     raise GradAvgError(_lib.GA_EINVAL, "gradient %d: need dense float32 on cuda:%s, got %s on %s, strides %s "
                                        "(no CPU fallback)" % (k % n, dev_index, g.dtype, g.device, tuple(g.stride())))

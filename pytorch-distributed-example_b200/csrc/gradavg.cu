@@ -966,6 +966,12 @@ int blocks_per_sm(ga_ctx *c, KernelFn fn, int variant) {
 int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int op, void *stream, int variant, bool direct,
            size_t byte_offset = 0) {
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
+    if (*(volatile int *)c->status_host != 0) {
+        // a kernel of this context already gave up on a peer: fail now instead of queueing more
+        // launches that would each spin until the timeout
+        c->broken = true;
+        return fail(GA_ETIMEOUT, "an earlier kernel timed out waiting for a peer rank's flag; the context is unusable");
+    }
     if (!c->opened) return fail(GA_ESTATE, "ga_open_peers has not been called");
     if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
     if (variant == GA_VARIANT_AUTO) {

@@ -117,3 +117,55 @@ def test_bucket_plan_reverse_order_and_cap():
     assert len(buckets) >= 2
     assert plan_buckets([10, 10], 1) == [[1], [0]]                      # a bucket always takes one tensor
     assert plan_buckets([], 1 << 20) == []
+
+
+def test_plan_cache_survives_id_reuse():
+    """The per-parameter-list layout cache is keyed by object identity; it must keep the objects
+    alive (ids of dead objects are recycled) and re-check sizes on every call."""
+    import ctypes
+    import threading
+    calls = []
+
+    class FakeLib:
+        def ga_average(self, ctx, ptrs, numel, n, stream, variant):
+            calls.append([numel[i] for i in range(n)])
+            return 0
+
+    class G:
+        def __init__(self, n):
+            self.n, self.dtype = n, torch.float32
+
+        def numel(self):
+            return self.n
+
+        def get_device(self):
+            return 0
+
+        def is_contiguous(self):
+            return True
+
+        def data_ptr(self):
+            return 4096
+
+    class P:
+        def __init__(self, n):
+            self.grad = G(n)
+
+    avg = ga.GradAverager.__new__(ga.GradAverager)
+    avg._lib, avg._ctx, avg._lock = FakeLib(), ctypes.c_void_p(1), threading.Lock()
+    avg._variant, avg._capacity, avg._local, avg.world_size, avg.rank = 0, 1 << 30, 0, 2, 0
+    avg._device, avg._dev_obj, avg._plans, avg._ptr_cache, avg._group = 0, torch.device("cuda", 0), {}, {}, None
+    orig = averager.torch.cuda.current_stream
+    averager.torch.cuda.current_stream = lambda d=None: type("S", (), {"cuda_stream": 0})()
+    try:
+        for step in range(200):                      # fresh objects every step: ids would be recycled
+            sizes = [3 + step % 7, 11]
+            avg.average_gradients([P(s) for s in sizes])
+            assert calls[-1] == sizes
+        ps = [P(5)]
+        avg.average_gradients(ps)
+        ps[0].grad = G(6)                            # same parameter object, gradient changed size
+        with pytest.raises(ga.GradAvgError):
+            avg.average_gradients(ps)
+    finally:
+        averager.torch.cuda.current_stream = orig
