@@ -75,6 +75,7 @@ class GradAverager:
             raise GradAvgError(_lib.GA_EINVAL, "world_size %d outside 1..%d" % (self.world_size, _lib.MAX_WORLD))
         self._device = device
         self._dev_obj = None
+        self._launch_base = 0
         self._ptr_cache = {}
         self._plans = {}
         if capacity_bytes:
@@ -144,6 +145,7 @@ class GradAverager:
                     dist.barrier(group=self._group)   # peers may still be reading my bucket
                     self._lib.ga_close_peers(self._ctx)
                     dist.barrier(group=self._group)   # nobody frees memory a peer still has mapped
+            self._launch_base += int(self._lib.ga_launch_count(self._ctx))
             self._lib.ga_destroy(self._ctx)
             self._ctx = None
             self._ptr_cache.clear()
@@ -358,7 +360,8 @@ class GradAverager:
 
     @property
     def launch_count(self):
-        return int(self._lib.ga_launch_count(self._ctx)) if self._ctx is not None else 0
+        """Kernels launched by this averager, across re-creations of its context."""
+        return self._launch_base + (int(self._lib.ga_launch_count(self._ctx)) if self._ctx is not None else 0)
 
     @property
     def last_grid(self):
