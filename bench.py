@@ -429,7 +429,7 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         bufs = [torch.randn(n, device=dev) for _ in range(2 if S >= (32 << 20) else 8)]
         k = [0]
         row = {"bytes": S}
-        for vname, v in (("oneshot", ga.ONESHOT), ("twoshot", ga.TWOSHOT), ("oneshot_push", ga.ONESHOT_PUSH),
+        for vname, v in (("auto", ga.AUTO), ("oneshot", ga.ONESHOT), ("twoshot", ga.TWOSHOT), ("oneshot_push", ga.ONESHOT_PUSH),
                          ("twoshot_push", ga.TWOSHOT_PUSH), ("twoshot_pipe", ga.TWOSHOT_PIPE)):
             if vname.startswith("oneshot") and S > (64 << 20) and world > 2:
                 continue
@@ -441,7 +441,9 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
                 avg.all_reduce_([[bufs[k[0] % len(bufs)]]], average=True, variant=v)
             med, best = timed(fused, iters)
             row["fused_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
-            if vname.endswith("_push") or vname.endswith("_pipe"):
+            if vname == "auto":
+                row["fused_auto"]["picked"] = avg.pick_variant(S)
+            if vname.endswith("_push") or vname.endswith("_pipe") or vname == "auto":
                 continue
             avg.bucket_acquire()
 
