@@ -422,6 +422,11 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         t = t.sort().values
         return float(t[iters // 2]) * 1e3, float(t[0]) * 1e3          # median, best (us)
 
+    # what the harness itself costs per iteration (Python call + event record, max over ranks): sizes
+    # whose times sit near this floor are host-bound, not kernel-bound
+    tiny = torch.zeros(8, device=dev)
+    floor_med, floor_best = timed(lambda: tiny.add_(1.0), 50)
+    out.append({"bytes": 0, "harness_floor_one_torch_launch": {"us": floor_med, "best_us": floor_best, "bus_gbps": 0.0}})
     for S in sizes:
         n = S // 4
         iters = 50 if S < (256 << 20) else 10
