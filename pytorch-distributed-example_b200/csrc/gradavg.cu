@@ -855,7 +855,8 @@ struct ga_ctx {
     int max_blocks_opt;
     int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
     size_t oneshot_max_bytes;
-    size_t pipe_min_bytes;          // AUTO: two-shot sets at least this large use the pipelined kernel
+    size_t pipe_min_bytes;          // AUTO: two-shot sets in [min, max] use the pipelined kernel: it pays while a
+    size_t pipe_max_bytes;          //   launch is two or three rounds (N=4/8 sweeps: 3-6 % at 32-128 MiB, a loss beyond)
     unsigned long long timeout_ns;
     int *status_host, *status_dev;
     Seg *seg_host[kSegRing], *seg_dev[kSegRing];
@@ -901,7 +902,8 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     if (world <= 2) c->oneshot_max_bytes = (size_t)-1;
     else if (n_local > 1) c->oneshot_max_bytes = (size_t)512 << 10;
     else c->oneshot_max_bytes = ((size_t)8 << 20) / (size_t)(world - 1);
-    c->pipe_min_bytes = (size_t)8 << 20;
+    c->pipe_min_bytes = (size_t)32 << 20;
+    c->pipe_max_bytes = (size_t)128 << 20;
     c->timeout_ns = 30ull * 1000000000ull;
     c->host_chunk_bytes = (size_t)8 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
@@ -1347,7 +1349,7 @@ int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
     if (c->n_local > 1 && c->n_local == c->world) return GA_VARIANT_HOSTED_DIRECT;
     if (c->n_local > 1 || c->world == 1) return one_shot ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     if (one_shot && nbytes * c->world <= c->capacity_bytes) return GA_VARIANT_ONESHOT_PUSH;
-    return nbytes >= c->pipe_min_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
+    return nbytes >= c->pipe_min_bytes && nbytes <= c->pipe_max_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
 }
 
 uint64_t ga_launch_count(const ga_ctx *c) { return c ? c->launches : 0; }
