@@ -67,6 +67,8 @@ extern "C" {
 #define GA_OPT_ONESHOT_MAX_BYTES 1   /* AUTO uses one-shot when bytes <= value */
 #define GA_OPT_TIMEOUT_MS        2   /* flag-wait timeout inside kernels; 0 = wait forever */
 #define GA_OPT_MAX_BLOCKS        3   /* cap on thread blocks per rank (0 = fill the device) */
+#define GA_OPT_TRACE             6   /* 1: the push kernels record per-block phase timestamps (globaltimer ns) */
+#define GA_OPT_HOST_CHUNK_BYTES  5   /* ga_average_host: largest chunk of the copy-in / reduce / copy-out pipeline */
 #define GA_OPT_PIPE_GROUP        4   /* TWOSHOT_PIPE: tile slots per block per round (0 = automatic) */
 
 typedef struct ga_ctx ga_ctx;
@@ -169,6 +171,15 @@ uint64_t ga_launch_count(const ga_ctx *ctx);
 int ga_last_grid(const ga_ctx *ctx, int *blocks, int *threads);
 
 int ga_set_option(ga_ctx *ctx, int option, int64_t value);
+
+/*
+ * Phase timestamps of the LAST launch (needs GA_OPT_TRACE): blocks * hosted ranks * slots words of
+ * %globaltimer nanoseconds, slot k of block b at out[(rank * blocks + b) * slots + k].  Slots of
+ * ga_push_kernel: 0 start, 1 previous call's readers gone, 2 scatter issued, 3 flags raised (stores
+ * acknowledged), 4 peers' flags seen, 5 fold + result stores issued, 6 flags raised, 7 peers' flags
+ * seen, 8 unpack done, 9 end.  ncu cannot profile a multi-rank run; this is the multi-GPU substitute.
+ */
+int ga_read_trace(ga_ctx *ctx, uint64_t *out, size_t max_words, int *blocks, int *slots);
 
 /* 0, or GA_ETIMEOUT once a kernel of this context gave up waiting for a peer (the context is
  * then unusable).  Reads a host-mapped word; call after synchronising the stream. */

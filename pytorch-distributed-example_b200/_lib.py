@@ -11,6 +11,8 @@ VARIANT_ONESHOT_PUSH, VARIANT_TWOSHOT_PUSH, VARIANT_TWOSHOT_PIPE = 3, 4, 5
 VARIANT_HOSTED_DIRECT = 6
 OP_F32_AVG, OP_I32_SUM, OP_F32_SUM = 0, 1, 2
 OPT_ONESHOT_MAX_BYTES, OPT_TIMEOUT_MS, OPT_MAX_BLOCKS, OPT_PIPE_GROUP = 1, 2, 3, 4
+OPT_HOST_CHUNK_BYTES = 5
+OPT_TRACE = 6
 IPC_HANDLE_BYTES = 64
 MAX_WORLD = 8
 TILE_BYTES = 2048
@@ -42,6 +44,8 @@ SIGNATURES = {
     "ga_launch_count": (_c.c_uint64, [_c.c_void_p]),
     "ga_last_grid": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_int)]),
     "ga_set_option": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int64]),
+    "ga_read_trace": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_uint64), _c.c_size_t, _c.POINTER(_c.c_int),
+                                 _c.POINTER(_c.c_int)]),
     "ga_status": (_c.c_int, [_c.c_void_p]),
     "ga_average_static": (_c.c_int, [_c.c_int, _c.c_int, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
                                      _c.c_void_p, _c.c_int]),

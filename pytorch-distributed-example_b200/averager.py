@@ -355,6 +355,16 @@ class GradAverager:
     def set_option(self, option, value):
         check(self._lib.ga_set_option(self._ctx, option, int(value)))
 
+    def read_trace(self):
+        """Phase timestamps of the last launch as an int64 array [hosted ranks, blocks, slots]
+        (needs set_option(OPT_TRACE, 1)); see ga_read_trace in include/gradavg.h."""
+        import numpy as np
+        buf = (ctypes.c_uint64 * (1024 * self.n_local * 16))()
+        b, k = ctypes.c_int(), ctypes.c_int()
+        check(self._lib.ga_read_trace(self._ctx, buf, len(buf), ctypes.byref(b), ctypes.byref(k)))
+        a = np.frombuffer(buf, dtype=np.uint64)[: self.n_local * b.value * k.value].astype(np.int64)
+        return a.reshape(self.n_local, b.value, k.value)
+
     def pick_variant(self, nbytes):
         return self._lib.ga_pick_variant(self._ctx, int(nbytes))
 

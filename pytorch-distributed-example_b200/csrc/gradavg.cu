@@ -37,6 +37,7 @@ constexpr int kThreads = 512;                  // 16 warps per block
 constexpr int kMaxBlocks = 1024;               // flag rows per rank
 constexpr int kInlineSegs = 128;               // pointer-table entries carried in kernel params
 constexpr int kSegRing = 4;                    // staging slots for larger pointer tables
+constexpr int kTraceSlots = 16;                // phase timestamps per block when tracing is on
 constexpr int kHostChunks = 64;                // most chunks one ga_average_host call is cut into
 
 typedef uint4 Vec;
@@ -70,6 +71,7 @@ struct Params {
     uint32_t epoch;
     int rank_base;
     int direct;                 // 1: bucket-direct (no pack, result -> recv)
+    unsigned long long *trace;  // optional phase timestamps, kTraceSlots per block (GA_OPT_TRACE)
     uint32_t rounds;            // pipelined two-shot push: rounds per launch (flags use epoch .. epoch+rounds-1)
     uint32_t group;             //   and tile slots per block per round
     Seg inline_segs[kInlineSegs];
@@ -116,6 +118,13 @@ __device__ __forceinline__ unsigned long long global_ns() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
+
+// Phase timestamp of this block (thread 0), only when the context has tracing switched on.
+#define GA_TRACE(p, k)                                                                                   \
+    do {                                                                                                 \
+        if ((p).trace && threadIdx.x == 0)                                                               \
+            (p).trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kTraceSlots + (k)] = global_ns(); \
+    } while (0)
 
 // Spin until *flag has reached `target` (wrap-safe).  Returns false on timeout.
 __device__ __forceinline__ bool spin_until(const uint32_t *flag, uint32_t target, unsigned long long timeout_ns) {
@@ -466,10 +475,12 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
 
     if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
     __syncthreads();
+    GA_TRACE(p, 0);
 
     // (0) every rank must have consumed the staging data of the previous call before anyone
     //     stores into it again (needed after a one-shot call; free when the ranks are in step)
     if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+    GA_TRACE(p, 1);
 
     // (1) scatter my gradient tiles into the owners' staging slots, nearest rank first
     if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
@@ -503,9 +514,12 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     }
 
     // (2) my column has landed everywhere / wait for everyone's column
+    GA_TRACE(p, 2);
     const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
     raise_flags<W>(p, ready_off, p.epoch);
+    GA_TRACE(p, 3);
     if (!wait_flags<W>(mypad->ready[b], p.epoch, p, &s_abort)) return;
+    GA_TRACE(p, 4);
 
     if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
         // (3) fold the W local slots of every tile straight into the gradient tensors
@@ -533,9 +547,12 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
                              });
         }
         // (4) my reduced column has landed everywhere / wait for everyone's
+        GA_TRACE(p, 5);
         const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
         raise_flags<W>(p, mid_off, p.epoch);
+        GA_TRACE(p, 6);
         if (!wait_flags<W>(mypad->mid[b], p.epoch, p, &s_abort)) return;
+        GA_TRACE(p, 7);
         // (5) unpack the other ranks' shards from my gather region (local traffic only)
         for (uint32_t i = first; i < Ts; i += stride) {
 #pragma unroll 1
@@ -555,6 +572,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
 
     // (6) this rank is done with its staging and gather data
     __syncthreads();
+    GA_TRACE(p, 8);
     if (threadIdx.x == 0) {
         __threadfence();
         s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
@@ -565,6 +583,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
         const size_t done_off = offsetof(Pad, done) / 4 + r;
         if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch);
     }
+    GA_TRACE(p, 9);
 }
 
 // Two-shot push, software-pipelined.  A block owns `group` tile slots per round; round q+1 is
@@ -853,6 +872,7 @@ struct ga_ctx {
     uint32_t epoch;                 // epoch of the last launch
     int sm_count, blocks_per_sm[8];                  // by variant; 0 = not queried yet
     int max_blocks_opt;
+    unsigned long long *trace_dev;  // GA_OPT_TRACE: kMaxBlocks * n_local * kTraceSlots words, or nullptr
     int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
     size_t oneshot_max_bytes;
     size_t pipe_min_bytes;          // AUTO: two-shot sets in [min, max] use the pipelined kernel: it pays while a
@@ -1013,6 +1033,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     p.epoch = c->epoch + 1;
     p.rank_base = c->rank_base;
     p.direct = direct ? 1 : 0;
+    p.trace = c->trace_dev;
 
     if (segs) {
         const size_t entries = (size_t)n_seg * c->n_local;
@@ -1275,7 +1296,11 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
     rc = drain_if_needed(c, stream);
     if (rc) return rc;
     const size_t bucket_bytes = (size_t)total * kTileBytes;
-    size_t chunk = c->host_chunk_bytes;
+    // Chunk = 1/32 of the set, between 1 MiB and host_chunk_bytes: the pipeline's fill and drain
+    // (first copy-in, last copy-out run alone) cost one chunk each.
+    size_t chunk = (bucket_bytes / 32 + kTileBytes - 1) / kTileBytes * kTileBytes;
+    if (chunk < ((size_t)1 << 20)) chunk = (size_t)1 << 20;
+    if (chunk > c->host_chunk_bytes) chunk = c->host_chunk_bytes;
     if ((bucket_bytes + chunk - 1) / chunk > (size_t)kHostChunks)
         chunk = ((bucket_bytes + kHostChunks - 1) / kHostChunks + kTileBytes - 1) / kTileBytes * kTileBytes;
     const int n_chunks = (int)((bucket_bytes + chunk - 1) / chunk);
@@ -1367,9 +1392,39 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
         case GA_OPT_ONESHOT_MAX_BYTES: c->oneshot_max_bytes = value < 0 ? 0 : (size_t)value; return GA_OK;
         case GA_OPT_TIMEOUT_MS: c->timeout_ns = value <= 0 ? 0 : (unsigned long long)value * 1000000ull; return GA_OK;
         case GA_OPT_MAX_BLOCKS: c->max_blocks_opt = value < 0 ? 0 : (int)value; return GA_OK;
+        case GA_OPT_TRACE: {
+            const size_t bytes = (size_t)kMaxBlocks * c->n_local * kTraceSlots * sizeof(unsigned long long);
+            if (value && !c->trace_dev) {
+                CUDA_TRY(cudaSetDevice(c->device));
+                CUDA_TRY(cudaMalloc((void **)&c->trace_dev, bytes));
+                CUDA_TRY(cudaMemset(c->trace_dev, 0, bytes));
+            } else if (!value && c->trace_dev) {
+                CUDA_TRY(cudaSetDevice(c->device));
+                CUDA_TRY(cudaDeviceSynchronize());
+                CUDA_TRY(cudaFree(c->trace_dev));
+                c->trace_dev = nullptr;
+            }
+            return GA_OK;
+        }
+        case GA_OPT_HOST_CHUNK_BYTES:
+            c->host_chunk_bytes = value < (int64_t)kTileBytes ? kTileBytes : ((size_t)value + kTileBytes - 1) / kTileBytes * kTileBytes;
+            return GA_OK;
         case GA_OPT_PIPE_GROUP: c->pipe_group_opt = value < 0 ? 0 : (value > 64 ? 64 : (int)value); return GA_OK;
     }
     return fail(GA_EINVAL, "unknown option %d", option);
+}
+
+int ga_read_trace(ga_ctx *c, uint64_t *out, size_t max_words, int *blocks, int *slots) {
+    if (!c || !out) return fail(GA_EINVAL, "NULL argument");
+    if (!c->trace_dev) return fail(GA_ESTATE, "tracing is off (ga_set_option(ctx, GA_OPT_TRACE, 1))");
+    const size_t words = (size_t)c->last_blocks * c->n_local * kTraceSlots;
+    if (words > max_words) return fail(GA_ECAPACITY, "trace needs %zu words, buffer has %zu", words, max_words);
+    CUDA_TRY(cudaSetDevice(c->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpy(out, c->trace_dev, words * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    if (blocks) *blocks = c->last_blocks;
+    if (slots) *slots = kTraceSlots;
+    return GA_OK;
 }
 
 int ga_status(ga_ctx *c) {
@@ -1416,6 +1471,7 @@ int ga_destroy(ga_ctx *c) {
     }
     if (c->status_host) cudaFreeHost(c->status_host);
     if (c->own_pads_dev) cudaFree(c->own_pads_dev);
+    if (c->trace_dev) cudaFree(c->trace_dev);
     if (c->s_in) {
         cudaStreamDestroy(c->s_in); cudaStreamDestroy(c->s_k); cudaStreamDestroy(c->s_out);
         cudaEventDestroy(c->ev_start); cudaEventDestroy(c->ev_done);
