@@ -629,17 +629,19 @@ def explore_pipe(avg, world, dev, dist):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.sort().values[iters // 2]) * 1e3
 
-    for S in (16 << 20, 64 << 20, 256 << 20):
+    mid = os.environ.get("GA_EXPLORE_MID") == "1"
+    for S in ((256 << 10, 1 << 20, 1724320, 4 << 20, 8 << 20) if mid else (16 << 20, 64 << 20, 256 << 20)):
         bufs = [torch.randn(S // 4, device=dev) for _ in range(3)]
         k = [0]
         row = {"bytes": S}
-        for vname, v in (("twoshot_push", ga.TWOSHOT_PUSH), ("twoshot", ga.TWOSHOT)):
+        for vname, v in (("twoshot_push", ga.TWOSHOT_PUSH), ("twoshot", ga.TWOSHOT)) + \
+                ((("oneshot_push", ga.ONESHOT_PUSH),) if mid and S * world <= avg.capacity else ()):
             def f():
                 k[0] += 1
                 avg.all_reduce_([[bufs[k[0] % 3]]], average=True, variant=v)
             row[vname] = round(timed(f), 1)
-        for blocks in (0, 148, 74):
-            for group in (0, 1, 2, 4, 8, 16):
+        for blocks in ((0,) if mid else (0, 148, 74)):
+            for group in ((1, 2, 4, 8, 16) if mid else (0, 1, 2, 4, 8, 16)):
                 avg.set_option(_lib.OPT_MAX_BLOCKS, blocks)
                 avg.set_option(_lib.OPT_PIPE_GROUP, group)
 
