@@ -875,8 +875,8 @@ struct ga_ctx {
     unsigned long long *trace_dev;  // GA_OPT_TRACE: kMaxBlocks * n_local * kTraceSlots words, or nullptr
     int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
     size_t oneshot_max_bytes;
-    size_t pipe_min_bytes;          // AUTO: two-shot sets in [min, max] use the pipelined kernel: it pays while a
-    size_t pipe_max_bytes;          //   launch is two or three rounds (N=4/8 sweeps: 3-6 % at 32-128 MiB, a loss beyond)
+    size_t pipe_min_bytes;          // pipelined kernel: one round below min, 32 MiB rounds from min on; AUTO stops
+    size_t pipe_max_bytes;          //   using it above max (N=4/8 sweeps: 3-10 % gain up to 128 MiB, a loss beyond)
     unsigned long long timeout_ns;
     int *status_host, *status_dev;
     Seg *seg_host[kSegRing], *seg_dev[kSegRing];
@@ -1065,17 +1065,28 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     int blocks = (int)((slots + wpb - 1) / wpb);
     uint32_t rounds = 1;
     if (variant == GA_VARIANT_TWOSHOT_PIPE) {
-        // Measured (profiles/r01b_explore_n8.md, r01e N=2): a round costs a flag round trip of a few
-        // tens of microseconds, so it must move >= ~32 MiB per GPU to hide it: one block per SM and
-        // `group` = 32 MiB / (world * 2 KiB * blocks) slots per block per round, at least 16.
-        if (c->max_blocks_opt == 0 && resident > c->sm_count / c->n_local) resident = c->sm_count / c->n_local;
-        if (resident < 1) resident = 1;
+        // Two regimes, both measured at 8 GPUs (profiles/r01b_explore_n8.md, r01d_explore_mid_n8.md):
+        //  * below pipe_min_bytes one round, and the slots spread over ~64 blocks (2..16 per block) so
+        //    that scatter, fold and unpack are each one or two items per warp instead of a serial
+        //    chain of W load->store steps;
+        //  * from pipe_min_bytes on, rounds of >= 32 MiB per GPU on one block per SM: a round costs a
+        //    flag round trip of a few tens of microseconds and must move enough bytes to hide it.
         uint32_t group = (uint32_t)c->pipe_group_opt;
-        if (group == 0) {
-            const size_t per_slot = (size_t)c->world * kTileBytes * (size_t)resident;
-            group = (uint32_t)((((size_t)32 << 20) + per_slot - 1) / per_slot);
-            if (group < 16) group = 16;
-            if (group > 64) group = 64;
+        if ((size_t)total_tiles * kTileBytes < c->pipe_min_bytes) {
+            if (group == 0) {
+                group = (slots + 63) / 64;
+                if (group < 2) group = 2;
+                if (group > 16) group = 16;
+            }
+        } else {
+            if (c->max_blocks_opt == 0 && resident > c->sm_count / c->n_local) resident = c->sm_count / c->n_local;
+            if (resident < 1) resident = 1;
+            if (group == 0) {
+                const size_t per_slot = (size_t)c->world * kTileBytes * (size_t)resident;
+                group = (uint32_t)((((size_t)32 << 20) + per_slot - 1) / per_slot);
+                if (group < 16) group = 16;
+                if (group > 64) group = 64;
+            }
         }
         blocks = (int)((slots + group - 1) / group);
         if (blocks > resident) blocks = resident;
@@ -1374,7 +1385,7 @@ int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
     if (c->n_local > 1 && c->n_local == c->world) return GA_VARIANT_HOSTED_DIRECT;
     if (c->n_local > 1 || c->world == 1) return one_shot ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     if (one_shot && nbytes * c->world <= c->capacity_bytes) return GA_VARIANT_ONESHOT_PUSH;
-    return nbytes >= c->pipe_min_bytes && nbytes <= c->pipe_max_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
+    return nbytes <= c->pipe_max_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
 }
 
 uint64_t ga_launch_count(const ga_ctx *c) { return c ? c->launches : 0; }
