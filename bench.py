@@ -537,6 +537,77 @@ def mnist_leg(avg, world, hosted, dev, dist, rank, steps=200, batch=128):
             dt = float(t)
         return steps / dt
 
+    def run_graphed(mode):
+        """Same step with forward, backward, averaging and Adam captured in ONE CUDA graph per
+        replica set (possible because the averaging kernel keeps its flag epoch on the device):
+        per step only the batch copy, the replay and loss.item() remain on the host."""
+        nets, opts, data = [], [], []
+        for l in range(hosted):
+            torch.manual_seed(0)
+            net = mnist_main.Net().to(dev)
+            nets.append(net)
+            opts.append(torch.optim.Adam(net.parameters(), lr=1e-3, capturable=True))
+            data.append(mnist_main.SyntheticBatches(steps + 10, batch, rank + l))
+        sx = [torch.zeros(batch, 1, 28, 28, device=dev) for _ in range(hosted)]
+        sy = [torch.zeros(batch, dtype=torch.long, device=dev) for _ in range(hosted)]
+        losses = [None] * hosted
+
+        def body():
+            for l in range(hosted):
+                loss = F.cross_entropy(nets[l](sx[l]), sy[l])
+                opts[l].zero_grad(set_to_none=False)
+                loss.backward()
+                losses[l] = loss
+            if mode == "ours":
+                if hosted == 1:
+                    avg.average_gradients(nets[0].parameters())
+                else:
+                    avg.average_gradients_local([n.parameters() for n in nets])
+            elif mode == "per_tensor_nccl":
+                for p in nets[0].parameters():
+                    dist.all_reduce(p.grad.data, op=dist.ReduceOp.SUM)
+                    p.grad.data /= float(world)
+            for l in range(hosted):
+                opts[l].step()
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            body()
+        iters = [iter(d) for d in data]
+
+        def one_step():
+            for l in range(hosted):
+                x, y = next(iters[l])
+                sx[l].copy_(x, non_blocking=True)
+                sy[l].copy_(y, non_blocking=True)
+            graph.replay()
+            return losses[hosted - 1].item()
+
+        for _ in range(10):
+            one_step()
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            one_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([dt], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t)
+        return steps / dt
+
     out = {"steps": steps, "batch_per_rank": batch, "world_size": world,
            "what": "mnist/main.py:84-99 step order, synthetic 128x1x28x28 batches from pinned host memory, Adam lr 1e-3"}
     out["ours"] = run("ours")
@@ -544,6 +615,12 @@ def mnist_leg(avg, world, hosted, dev, dist, rank, steps=200, batch=128):
         out["per_tensor_nccl"] = run("per_tensor_nccl")
     else:
         out["no_averaging_same_replicas"] = run("none")
+    try:
+        out["graphed_step_ours"] = run_graphed("ours")
+        if dist is not None:
+            out["graphed_step_per_tensor_nccl"] = run_graphed("per_tensor_nccl")
+    except Exception as e:                                   # report, never fake
+        out["graphed_step_error"] = "%s: %s" % (type(e).__name__, str(e)[:300])
     return out
 
 

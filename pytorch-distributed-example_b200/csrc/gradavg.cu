@@ -53,7 +53,10 @@ struct Pad {                                    // head of every rank's IPC allo
     uint32_t mid[kMaxBlocks][kMaxWorld];        // [block][src rank]: src reduced its shard (epoch)
     uint32_t done[kMaxWorld];                   // [src rank]: src finished reading my bucket (epoch)
     uint32_t finished_blocks;                   // local block counter of the running launch
-    uint32_t reserved[23];
+    uint32_t epoch;                             // last flag value this rank used; read at kernel start, advanced
+                                                // by the last block, so a launch carries no host-side counter
+                                                // and can be replayed from a CUDA graph
+    uint32_t reserved[22];
 };
 constexpr size_t kPadBytes = (sizeof(Pad) + 4095) / 4096 * 4096;
 
@@ -68,7 +71,6 @@ struct Params {
     uint32_t n_seg;
     uint32_t total_tiles;
     uint32_t shard_tiles;       // two-shot: tiles per rank shard
-    uint32_t epoch;
     int rank_base;
     int direct;                 // 1: bucket-direct (no pack, result -> recv)
     unsigned long long *trace;  // optional phase timestamps, kTraceSlots per block (GA_OPT_TRACE)
@@ -302,6 +304,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     const float wf = (float)W;
 
     Pad *mypad = p.pad[r];
+    const uint32_t epoch = ld_relaxed_sys(&mypad->epoch) + 1;     // same value in every block of this launch
     Vec *mysend = (Vec *)p.send[r];
     Sink sink;
     sink.n_seg = (int)p.n_seg;
@@ -314,7 +317,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     // (0) The previous call's readers must be done with my bucket before pack overwrites it.
     //     (Bucket-direct calls end with this wait instead, see the bottom.)
     if (!p.direct) {
-        if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+        if (!wait_flags<W>(mypad->done, epoch - 1, p, &s_abort)) return;
     }
 
     // (1) pack: gradient tensors -> my bucket
@@ -344,8 +347,8 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
 
     // (2) barrier 1: my column is packed / wait for the same column of every rank
     const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
-    raise_flags<W>(p, ready_off, p.epoch);
-    if (!wait_flags<W>(mypad->ready[b], p.epoch, p, &s_abort)) return;
+    raise_flags<W>(p, ready_off, epoch);
+    if (!wait_flags<W>(mypad->ready[b], epoch, p, &s_abort)) return;
 
     if (VARIANT == GA_VARIANT_ONESHOT) {
         // (3) every rank reduces every tile and writes its own copy of the result
@@ -367,8 +370,8 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
         }
         // (4) barrier 2: shard column reduced everywhere
         const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
-        raise_flags<W>(p, mid_off, p.epoch);
-        if (!wait_flags<W>(mypad->mid[b], p.epoch, p, &s_abort)) return;
+        raise_flags<W>(p, mid_off, epoch);
+        if (!wait_flags<W>(mypad->mid[b], epoch, p, &s_abort)) return;
         // (5) all-gather: pull the other ranks' reduced shards, starting with the next rank so
         //     that at any moment the W ranks read from W different sources
         for (uint32_t i = first; i < p.shard_tiles; i += stride) {
@@ -397,10 +400,10 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     }
     __syncthreads();
     if (s_last) {
-        if (threadIdx.x == 0) mypad->finished_blocks = 0;
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch);
-        if (p.direct) wait_flags<W>(mypad->done, p.epoch, p, &s_abort);
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
+        if (p.direct) wait_flags<W>(mypad->done, epoch, p, &s_abort);
     }
 }
 
@@ -466,6 +469,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     const float wf = (float)W;
 
     Pad *mypad = p.pad[r];
+    const uint32_t epoch = ld_relaxed_sys(&mypad->epoch) + 1;     // same value in every block of this launch
     Vec *mystage = (Vec *)p.send[r];
     Vec *mygather = (Vec *)p.gather[r];
     Sink sink;
@@ -479,7 +483,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
 
     // (0) every rank must have consumed the staging data of the previous call before anyone
     //     stores into it again (needed after a one-shot call; free when the ranks are in step)
-    if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+    if (!wait_flags<W>(mypad->done, epoch - 1, p, &s_abort)) return;
     GA_TRACE(p, 1);
 
     // (1) scatter my gradient tiles into the owners' staging slots, nearest rank first
@@ -516,9 +520,9 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     // (2) my column has landed everywhere / wait for everyone's column
     GA_TRACE(p, 2);
     const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
-    raise_flags<W>(p, ready_off, p.epoch);
+    raise_flags<W>(p, ready_off, epoch);
     GA_TRACE(p, 3);
-    if (!wait_flags<W>(mypad->ready[b], p.epoch, p, &s_abort)) return;
+    if (!wait_flags<W>(mypad->ready[b], epoch, p, &s_abort)) return;
     GA_TRACE(p, 4);
 
     if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
@@ -549,9 +553,9 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
         // (4) my reduced column has landed everywhere / wait for everyone's
         GA_TRACE(p, 5);
         const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
-        raise_flags<W>(p, mid_off, p.epoch);
+        raise_flags<W>(p, mid_off, epoch);
         GA_TRACE(p, 6);
-        if (!wait_flags<W>(mypad->mid[b], p.epoch, p, &s_abort)) return;
+        if (!wait_flags<W>(mypad->mid[b], epoch, p, &s_abort)) return;
         GA_TRACE(p, 7);
         // (5) unpack the other ranks' shards from my gather region (local traffic only)
         for (uint32_t i = first; i < Ts; i += stride) {
@@ -579,9 +583,9 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     }
     __syncthreads();
     if (s_last) {
-        if (threadIdx.x == 0) mypad->finished_blocks = 0;
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch);
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
     }
     GA_TRACE(p, 9);
 }
@@ -609,6 +613,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
     const float wf = (float)W;
 
     Pad *mypad = p.pad[r];
+    const uint32_t epoch = ld_relaxed_sys(&mypad->epoch) + 1;     // first round's flag value
     const Vec *mystage = (const Vec *)p.send[r];
     const Vec *mygather = (const Vec *)p.gather[r];
     const Seg *segs = (p.dev_segs ? p.dev_segs : p.inline_segs) + (size_t)ly * p.n_seg;
@@ -618,7 +623,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
 
     if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
     __syncthreads();
-    if (!wait_flags<W>(mypad->done, p.epoch - 1, p, &s_abort)) return;
+    if (!wait_flags<W>(mypad->done, epoch - 1, p, &s_abort)) return;
 
     auto slot0 = [&](int q) { return ((uint32_t)q * gridDim.x + b) * G; };
 
@@ -689,21 +694,21 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
     };
 
     scatter(0);
-    raise_flags<W>(p, ready_off, p.epoch);
+    raise_flags<W>(p, ready_off, epoch);
     for (int q = 0; q < R; ++q) {
         if (q + 1 < R) {
             scatter(q + 1);
-            raise_flags<W>(p, ready_off, p.epoch + q + 1);
+            raise_flags<W>(p, ready_off, epoch + q + 1);
         }
-        if (!wait_flags<W>(mypad->ready[b], p.epoch + q, p, &s_abort)) return;
+        if (!wait_flags<W>(mypad->ready[b], epoch + q, p, &s_abort)) return;
         fold(q);
-        raise_flags<W>(p, mid_off, p.epoch + q);
+        raise_flags<W>(p, mid_off, epoch + q);
         if (q > 0) {
-            if (!wait_flags<W>(mypad->mid[b], p.epoch + q - 1, p, &s_abort)) return;
+            if (!wait_flags<W>(mypad->mid[b], epoch + q - 1, p, &s_abort)) return;
             unpack(q - 1);
         }
     }
-    if (!wait_flags<W>(mypad->mid[b], p.epoch + R - 1, p, &s_abort)) return;
+    if (!wait_flags<W>(mypad->mid[b], epoch + R - 1, p, &s_abort)) return;
     unpack(R - 1);
 
     __syncthreads();
@@ -713,9 +718,9 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
     }
     __syncthreads();
     if (s_last) {
-        if (threadIdx.x == 0) mypad->finished_blocks = 0;
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch + R - 1; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, p.epoch + R - 1);
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch + R - 1);
     }
 }
 
@@ -782,10 +787,11 @@ __global__ void __launch_bounds__(kThreads, 2) ga_hosted_direct_kernel(const __g
 // Launched only when a bucket-direct call follows a tensor-list call: the caller is about to
 // overwrite the bucket from the host side of the stream, so every peer must have finished
 // reading it (tensor-list calls check this lazily, at the start of the NEXT kernel).
-__global__ void ga_drain_kernel(const Pad *const *pads, int n_local, int world, uint32_t epoch,
+__global__ void ga_drain_kernel(const Pad *const *pads, int n_local, int world,
                                 unsigned long long timeout_ns, int *status) {
     const int l = threadIdx.x / kMaxWorld, src = threadIdx.x % kMaxWorld;
     if (l < n_local && src < world) {
+        const uint32_t epoch = ld_relaxed_sys(&pads[l]->epoch);     // last value this rank's kernels used
         if (!spin_until(&pads[l]->done[src], epoch, timeout_ns)) *(volatile int *)status = GA_ETIMEOUT;
     }
 }
@@ -869,7 +875,6 @@ struct ga_ctx {
     void *gather_all[kMaxWorld];    // by global rank (second half of the IPC allocation)
     Pad *pad_all[kMaxWorld];        // by global rank
     bool opened, broken;
-    uint32_t epoch;                 // epoch of the last launch
     int sm_count, blocks_per_sm[8];                  // by variant; 0 = not queried yet
     int max_blocks_opt;
     unsigned long long *trace_dev;  // GA_OPT_TRACE: kMaxBlocks * n_local * kTraceSlots words, or nullptr
@@ -1030,7 +1035,6 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     p.n_seg = n_seg;
     p.total_tiles = total_tiles;
     p.shard_tiles = (total_tiles + c->world - 1) / c->world;
-    p.epoch = c->epoch + 1;
     p.rank_base = c->rank_base;
     p.direct = direct ? 1 : 0;
     p.trace = c->trace_dev;
@@ -1121,7 +1125,6 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     } else {
         CUDA_TRY(cudaLaunchKernel((const void *)fn, grid, block, args, 0, st));
     }
-    c->epoch += rounds;
     c->launches += 1;
     c->last_was_tensor_call = !direct;
     c->last_blocks = blocks;
@@ -1135,7 +1138,7 @@ int drain_if_needed(ga_ctx *c, void *stream) {
     if (!c->last_was_tensor_call) return GA_OK;
     CUDA_TRY(cudaSetDevice(c->device));
     ga_drain_kernel<<<1, kMaxWorld * kMaxWorld, 0, (cudaStream_t)stream>>>(
-        c->own_pads_dev, c->n_local, c->world, c->epoch, c->timeout_ns, c->status_dev);
+        c->own_pads_dev, c->n_local, c->world, c->timeout_ns, c->status_dev);
     CUDA_TRY(cudaGetLastError());
     c->launches += 1;
     c->last_was_tensor_call = false;
@@ -1576,7 +1579,6 @@ extern "C" int ga_average_static(int world, int device, const void *const *grad_
     p.n_seg = (uint32_t)n_tensors;
     p.total_tiles = (uint32_t)total;
     p.shard_tiles = ((uint32_t)total + world - 1) / world;
-    p.epoch = 1;
     p.rank_base = 0;
     p.direct = 0;
     for (int l = 0; l < world; ++l) {

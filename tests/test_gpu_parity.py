@@ -442,3 +442,49 @@ def test_python_layer_layouts_and_errors(built):
             avg.average_gradients_local([[nog], [nog]])
     finally:
         avg.close()
+
+
+@pytest.mark.parametrize("variant", ["auto", "twoshot", "twoshot_push", "twoshot_pipe", "oneshot_push"])
+def test_cuda_graph_replay(built, variant):
+    """The flag epoch lives in device memory, so a captured launch can be replayed: capture one
+    averaging of static gradient tensors in a CUDA graph, replay it on fresh contents five times,
+    interleaved with an eager call, and compare every result with the rank-order fold."""
+    import pytorch_distributed_example_b200 as ga
+    torch.cuda.set_device(0)
+    world = 3
+    shapes = oracle.MINI_SHAPES
+    avg = ga.GradAverager(local_world=world, device=0, capacity_bytes=1 << 20)
+
+    class P:
+        def __init__(self, g):
+            self.grad = g
+    static = [[P(torch.zeros(s, device="cuda")) for s in shapes] for _ in range(world)]
+    try:
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(2):                                   # warm-up outside capture (allocations, occupancy queries)
+                avg.average_gradients_local(static, variant=variant)
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            avg.average_gradients_local(static, variant=variant)
+        for rep in range(5):
+            host = [[t.numpy() for t in oracle.seeded_grads(shapes, r, 500 + 10 * rep)] for r in range(world)]
+            for r in range(world):
+                for p, h in zip(static[r], host[r]):
+                    p.grad.copy_(torch.from_numpy(h))
+            g.replay()
+            torch.cuda.synchronize()
+            want = _fold(host, world)
+            for r in range(world):
+                for p, w in zip(static[r], want):
+                    assert p.grad.cpu().numpy().tobytes() == w.tobytes(), "replay %d" % rep
+            if rep == 2:                                          # an eager call between replays keeps the epochs in step
+                dev = _to_dev(host)
+                avg.all_reduce_(dev, average=True, variant=variant)
+                _assert_all_ranks_equal(dev, want, "eager between replays")
+        avg.check_status()
+    finally:
+        avg.close()
