@@ -464,6 +464,10 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
             b.div_(float(world))
         med, best = timed(nccl, iters)
         row["nccl_allreduce_div"] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+        if S <= (4 << 20):
+            # host-free latency: 20 back-to-back calls captured in one CUDA graph, replayed
+            row["graph_auto"] = graph_latency(lambda b: avg.all_reduce_([[b]], average=True), bufs, dev, dist)
+            row["graph_nccl_allreduce_div"] = graph_latency(lambda b: (dist.all_reduce(b), b.div_(float(world))), bufs, dev, dist)
         out.append(row)
         del bufs
         avg.check_status()
@@ -733,6 +737,39 @@ def explore_pipe(avg, world, dev, dist):
         out.append(row)
         del bufs
     return out
+
+
+def graph_latency(call, bufs, dev, dist, calls=20, replays=6):
+    """us per call with the host out of the way: `calls` back-to-back invocations captured in one
+    CUDA graph (possible for our kernels because their flag epoch lives on the device), replayed
+    `replays` times; median replay time / calls, max over ranks."""
+    import torch
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for i in range(3):
+            call(bufs[i % len(bufs)])
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    dist.barrier()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(calls):
+            call(bufs[i % len(bufs)])
+    times = []
+    for _ in range(replays):
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1) * 1e3 / calls)
+    t = torch.tensor(times, device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    t = t.sort().values
+    return {"us": float(t[len(times) // 2]), "best_us": float(t[0]), "bus_gbps": 0.0}
 
 
 def load_traffic():
