@@ -133,7 +133,7 @@ class GradAverager:
         if self._ctx is not None:
             # Every rank sees the same sizes, so every rank takes this branch in the same call.
             self.close()
-        self._create(max(need_bytes, 8 << 20))      # room for one-shot staging of small sets
+        self._create(max(need_bytes, 32 << 20))     # room for two one-shot staging halves of small sets
 
     def close(self):
         if self._ctx is not None:

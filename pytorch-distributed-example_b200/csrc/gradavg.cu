@@ -56,7 +56,9 @@ struct Pad {                                    // head of every rank's IPC allo
     uint32_t epoch;                             // last flag value this rank used; read at kernel start, advanced
                                                 // by the last block, so a launch carries no host-side counter
                                                 // and can be replayed from a CUDA graph
-    uint32_t reserved[22];
+    uint32_t last_kind;                         // 1 if this rank's previous launch was a double-buffered one-shot
+                                                // push (its successor of the same kind need not wait for `done`)
+    uint32_t reserved[21];
 };
 constexpr size_t kPadBytes = (sizeof(Pad) + 4095) / 4096 * 4096;
 
@@ -73,6 +75,7 @@ struct Params {
     uint32_t shard_tiles;       // two-shot: tiles per rank shard
     int rank_base;
     int direct;                 // 1: bucket-direct (no pack, result -> recv)
+    unsigned long long parity_stride;   // one-shot push: byte offset of the odd-epoch staging half (0 = single buffer)
     unsigned long long *trace;  // optional phase timestamps, kTraceSlots per block (GA_OPT_TRACE)
     uint32_t rounds;            // pipelined two-shot push: rounds per launch (flags use epoch .. epoch+rounds-1)
     uint32_t group;             //   and tile slots per block per round
@@ -400,7 +403,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     }
     __syncthreads();
     if (s_last) {
-        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; }
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = 0; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
         if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
         if (p.direct) wait_flags<W>(mypad->done, epoch, p, &s_abort);
@@ -583,7 +586,99 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     }
     __syncthreads();
     if (s_last) {
-        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; }
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = 0; }
+        const size_t done_off = offsetof(Pad, done) / 4 + r;
+        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
+    }
+    GA_TRACE(p, 9);
+}
+
+// One-shot push, latency form.  A block owns `group` consecutive tiles; the scatter is spread over
+// the warps as (tile, destination) items and the fold as (tile, 512-byte row) items, so a small set
+// still engages many SMs.  With room for two staging halves (parity_stride != 0) consecutive
+// launches alternate halves by epoch parity: a peer can then never be overwritten while it is still
+// folding the previous call, so such a launch skips the wait for the peers' `done` words whenever
+// this rank's previous launch was of the same kind (recorded in the pad, so it also holds under
+// graph replay).  Any other predecessor (a pull kernel's readers, a two-shot's staging) is waited for.
+template <int W, int OP>
+__global__ void __launch_bounds__(kThreads, 2) ga_push1_kernel(const __grid_constant__ Params p) {
+    __shared__ int s_abort;
+    __shared__ int s_last;
+    const int ly = blockIdx.y;
+    const int r = p.rank_base + ly;
+    const int b = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t wpb = blockDim.x >> 5;
+    const uint32_t T = p.total_tiles, G = p.group;
+    const float wf = (float)W;
+    const uint32_t t0 = b * G;
+    const uint32_t nt = t0 >= T ? 0u : (T - t0 < G ? T - t0 : G);
+
+    Pad *mypad = p.pad[r];
+    const uint32_t epoch = ld_relaxed_sys(&mypad->epoch) + 1;
+    const bool dbuf = p.parity_stride != 0;
+    const size_t half = dbuf && (epoch & 1u) ? (size_t)p.parity_stride : 0;
+    const Vec *mystage = (const Vec *)((const char *)p.send[r] + half);
+    const Seg *segs = (p.dev_segs ? p.dev_segs : p.inline_segs) + (size_t)ly * p.n_seg;
+    const int n_seg = (int)p.n_seg;
+
+    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
+    __syncthreads();
+    GA_TRACE(p, 0);
+    if (!(dbuf && ld_relaxed_sys(&mypad->last_kind) == 1u)) {
+        if (!wait_flags<W>(mypad->done, epoch - 1, p, &s_abort)) return;
+    }
+    GA_TRACE(p, 1);
+
+    for (uint32_t it = warp; it < nt * W; it += wpb) {
+        const uint32_t t = t0 + it / W;
+        const int j = (r + (int)(it % W)) % W;
+        const Seg sg = segs[find_seg(segs, n_seg, t)];
+        Vec v[kLaneVecs];
+        load_grad_tile(sg, t, lane, v);
+        Vec *dst = (Vec *)((char *)p.send[j] + half) + ((size_t)r * T + t) * kTileVecs + lane;
+#pragma unroll
+        for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+    }
+    GA_TRACE(p, 2);
+    const size_t ready_off = offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + r;
+    raise_flags<W>(p, ready_off, epoch);
+    GA_TRACE(p, 3);
+    if (!wait_flags<W>(mypad->ready[b], epoch, p, &s_abort)) return;
+    GA_TRACE(p, 4);
+
+    for (uint32_t it = warp; it < nt * kLaneVecs; it += wpb) {
+        const uint32_t t = t0 + it / kLaneVecs;
+        const int u = (int)(it % kLaneVecs);
+        const Seg sg = segs[find_seg(segs, n_seg, t)];
+        Vec v[W];
+#pragma unroll
+        for (int s = 0; s < W; ++s) v[s] = __ldcg(mystage + ((size_t)s * T + t) * kTileVecs + u * 32 + lane);
+        Vec acc[1] = {v[0]};
+#pragma unroll
+        for (int s = 1; s < W; ++s) {              // ((g0 + g1) + g2) + ...
+            acc[0].x = ElemOp<OP>::add(acc[0].x, v[s].x);
+            acc[0].y = ElemOp<OP>::add(acc[0].y, v[s].y);
+            acc[0].z = ElemOp<OP>::add(acc[0].z, v[s].z);
+            acc[0].w = ElemOp<OP>::add(acc[0].w, v[s].w);
+        }
+        acc[0].x = ElemOp<OP>::fin(acc[0].x, wf);
+        acc[0].y = ElemOp<OP>::fin(acc[0].y, wf);
+        acc[0].z = ElemOp<OP>::fin(acc[0].z, wf);
+        acc[0].w = ElemOp<OP>::fin(acc[0].w, wf);
+        store_grad_vecs<1>(sg, t, lane, u, acc);
+    }
+
+    __syncthreads();
+    GA_TRACE(p, 8);
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = dbuf ? 1u : 0u; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
         if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
     }
@@ -718,7 +813,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
     }
     __syncthreads();
     if (s_last) {
-        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch + R - 1; }
+        if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch + R - 1; mypad->last_kind = 0; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
         if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch + R - 1);
     }
@@ -828,6 +923,11 @@ template <int W, int VARIANT> KernelFn pick_push_op(int op) {
            : op == GA_OP_F32_SUM ? (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_SUM>
                                  : (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_AVG>;
 }
+template <int W> KernelFn pick_push1_op(int op) {
+    return op == GA_OP_I32_SUM   ? (KernelFn)ga_push1_kernel<W, GA_OP_I32_SUM>
+           : op == GA_OP_F32_SUM ? (KernelFn)ga_push1_kernel<W, GA_OP_F32_SUM>
+                                 : (KernelFn)ga_push1_kernel<W, GA_OP_F32_AVG>;
+}
 template <int W> KernelFn pick_pipe_op(int op) {
     return op == GA_OP_I32_SUM   ? (KernelFn)ga_push_pipe_kernel<W, GA_OP_I32_SUM>
            : op == GA_OP_F32_SUM ? (KernelFn)ga_push_pipe_kernel<W, GA_OP_F32_SUM>
@@ -843,7 +943,7 @@ template <int W> KernelFn pick_variant(int variant, int op) {
         case GA_VARIANT_HOSTED_DIRECT: return pick_hosted_op<W>(op);
         case GA_VARIANT_TWOSHOT_PIPE: return pick_pipe_op<W>(op);
         case GA_VARIANT_TWOSHOT: return pick_op<W, GA_VARIANT_TWOSHOT>(op);
-        case GA_VARIANT_ONESHOT_PUSH: return pick_push_op<W, GA_VARIANT_ONESHOT_PUSH>(op);
+        case GA_VARIANT_ONESHOT_PUSH: return pick_push1_op<W>(op);
         case GA_VARIANT_TWOSHOT_PUSH: return pick_push_op<W, GA_VARIANT_TWOSHOT_PUSH>(op);
     }
     return pick_op<W, GA_VARIANT_ONESHOT>(op);
@@ -1098,6 +1198,18 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
         rounds = (slots + (uint32_t)blocks * group - 1) / ((uint32_t)blocks * group);
         if (rounds < 1) rounds = 1;
         p.group = group;
+    }
+    if (variant == GA_VARIANT_ONESHOT_PUSH) {
+        // one block per `group` tiles, as many blocks as are resident; two staging halves if they fit
+        uint32_t group = (total_tiles + (uint32_t)resident - 1) / (uint32_t)resident;
+        if (group < 1) group = 1;
+        blocks = (int)((total_tiles + group - 1) / group);
+        p.group = group;
+        // The odd half starts at a FIXED offset (middle of the bucket), whatever the set size: with a
+        // size-dependent offset a smaller set's odd half could land inside a larger predecessor's even half.
+        const size_t one = (size_t)total_tiles * kTileBytes * c->world;
+        const size_t mid = c->capacity_bytes / 2 / kTileBytes * kTileBytes;
+        p.parity_stride = one <= mid ? mid : 0;
     }
     p.rounds = rounds;
     if (blocks > resident) blocks = resident;
