@@ -1201,8 +1201,10 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     }
     if (variant == GA_VARIANT_ONESHOT_PUSH) {
         // one block per `group` tiles, as many blocks as are resident; two staging halves if they fit
+        // at least 16 (tile, destination) items per block so that every warp scatters
         uint32_t group = (total_tiles + (uint32_t)resident - 1) / (uint32_t)resident;
-        if (group < 1) group = 1;
+        const uint32_t min_group = (uint32_t)((kThreads / 32 + c->world - 1) / c->world);
+        if (group < min_group) group = min_group;
         blocks = (int)((total_tiles + group - 1) / group);
         p.group = group;
         // The odd half starts at a FIXED offset (middle of the bucket), whatever the set size: with a
