@@ -1203,7 +1203,9 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
         // one block per `group` tiles, as many blocks as are resident; two staging halves if they fit
         // at least 16 (tile, destination) items per block so that every warp scatters
         uint32_t group = (total_tiles + (uint32_t)resident - 1) / (uint32_t)resident;
-        const uint32_t min_group = (uint32_t)((kThreads / 32 + c->world - 1) / c->world);
+        // (one item per warp up to 2 MiB, two beyond: N=2 sweeps r01k/r01l)
+        const uint32_t per_block = total_tiles <= 1024 ? kThreads / 32 : 2 * (kThreads / 32);
+        const uint32_t min_group = (per_block + (uint32_t)c->world - 1) / (uint32_t)c->world;
         if (group < min_group) group = min_group;
         blocks = (int)((total_tiles + group - 1) / group);
         p.group = group;
