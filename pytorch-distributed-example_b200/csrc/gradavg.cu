@@ -145,27 +145,41 @@ __device__ __forceinline__ bool spin_until(const uint32_t *flag, uint32_t target
     return true;
 }
 
-// Block-wide: threads 0..W-1 each wait for one source rank's flag, then everyone syncs.
-// Returns false (for the whole block) if any wait timed out.
+// Block-wide wait for one flag per source rank.  ONE thread polls the W words in turn (they turn
+// up within a round trip of each other) and issues ONE system-scope fence: with eight polling
+// threads each needed its own fence, and system fences are what these barriers cost (more blocks
+// made every variant slower until this was changed).  Returns false for the whole block on timeout.
 template <int W>
 __device__ __forceinline__ bool wait_flags(const uint32_t *row, uint32_t target, const Params &p, int *s_abort) {
-    if (threadIdx.x < W) {
-        if (!spin_until(row + threadIdx.x, target, p.timeout_ns)) {
-            *s_abort = 1;
-            *(volatile int *)p.status = GA_ETIMEOUT;
+    if (threadIdx.x == 0) {
+#pragma unroll 1
+        for (int s = 0; s < W; ++s) {
+            if (!spin_until(row + s, target, p.timeout_ns)) {
+                *s_abort = 1;
+                *(volatile int *)p.status = GA_ETIMEOUT;
+                break;
+            }
         }
-        asm volatile("fence.acq_rel.sys;" ::: "memory");   // acquire: peers' data before our loads of it
+        asm volatile("fence.acq_rel.sys;" ::: "memory");   // acquire: peers' data before the block's loads of it
     }
     __syncthreads();
     return *s_abort == 0;
 }
 
-// Block-wide: everything this block wrote so far becomes visible, then flag `col` of row
-// `row_off` is raised in every rank's pad.
+__device__ __forceinline__ void st_relaxed_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Block-wide: everything this block wrote so far becomes visible (one system-scope fence by one
+// thread, after the block barrier), then that thread posts the flag word into every rank's pad.
 template <int W>
 __device__ __forceinline__ void raise_flags(const Params &p, size_t word_off, uint32_t value) {
     __syncthreads();
-    if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + word_off, value);
+    if (threadIdx.x == 0) {
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + word_off, value);
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -405,7 +419,11 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     if (s_last) {
         if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = 0; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
+        if (threadIdx.x == 0) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + done_off, epoch);
+        }
         if (p.direct) wait_flags<W>(mypad->done, epoch, p, &s_abort);
     }
 }
@@ -588,7 +606,11 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     if (s_last) {
         if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = 0; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
+        if (threadIdx.x == 0) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + done_off, epoch);
+        }
     }
     GA_TRACE(p, 9);
 }
@@ -680,7 +702,11 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push1_kernel(const __grid_cons
     if (s_last) {
         if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = dbuf ? 1u : 0u; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch);
+        if (threadIdx.x == 0) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + done_off, epoch);
+        }
     }
     GA_TRACE(p, 9);
 }
@@ -815,7 +841,11 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_pipe_kernel(const __grid_
     if (s_last) {
         if (threadIdx.x == 0) { mypad->finished_blocks = 0; mypad->epoch = epoch + R - 1; mypad->last_kind = 0; }
         const size_t done_off = offsetof(Pad, done) / 4 + r;
-        if (threadIdx.x < W) st_release_sys((uint32_t *)p.pad[threadIdx.x] + done_off, epoch + R - 1);
+        if (threadIdx.x == 0) {
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+#pragma unroll
+            for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + done_off, epoch + R - 1);
+        }
     }
 }
 
