@@ -1054,7 +1054,7 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     // AUTO thresholds, from the round-1 sweeps (profiles/): hosted worlds move everything through
     // HBM and prefer the pull kernels; across GPUs the push kernels win at every size, one-shot
     // while its (world-1)*S egress stays below ~8 MiB.
-    if (world <= 2) c->oneshot_max_bytes = (size_t)64 << 20;   // same link bytes either way; two-shot stages less
+    if (world <= 2) c->oneshot_max_bytes = (size_t)32 << 20;   // same link bytes either way; two-shot stages less (r01m sweep)
     else if (n_local > 1) c->oneshot_max_bytes = (size_t)512 << 10;
     else c->oneshot_max_bytes = ((size_t)8 << 20) / (size_t)(world - 1);
     c->pipe_min_bytes = (size_t)32 << 20;
