@@ -110,9 +110,6 @@ template <> struct ElemOp<GA_OP_I32_SUM> {
 // ------------------------------------------------------------------------------------------
 // flags
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
 __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
     uint32_t v;
     asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
