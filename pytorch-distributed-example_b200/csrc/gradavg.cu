@@ -2,18 +2,27 @@
 //
 // The one hot path of dblakely/pytorch-distributed-example, /root/reference/mnist/main.py:122-127
 // (all_reduce(SUM) of every p.grad, then /= float(world_size)) and toy/main.py:19-20, as ONE
-// fused kernel per call:
+// fused kernel per call.  Two families:
 //
-//   pack   gather the per-parameter gradients into this rank's flat bucket (16-byte vectors,
-//          every tensor padded to a 2 KiB tile so a warp-tile never straddles two tensors)
-//   flag   per-block release/acquire flags written straight into the peers' memory
-//   reduce read the peers' buckets over NVLink (plain ld.global on CUDA-IPC mapped pointers),
-//          add in rank order, divide by (float)world  -- one-shot: every rank reads everything;
-//          two-shot: rank r reduces shard r in place, then every rank pulls the other shards
-//   unpack write the result straight into the gradient tensors (no second pass)
+//   pull  ga_fused_kernel        pack the gradients into this rank's flat bucket (16-byte vectors,
+//                                every tensor padded to a 2 KiB tile so a warp tile never straddles
+//                                two tensors) -> per-block flags -> LOAD the peers' buckets over
+//                                NVLink (plain ld.global on CUDA-IPC mapped pointers), add in rank
+//                                order, divide by (float)world, write straight into the gradients.
+//                                One-shot: every rank reads everything; two-shot: rank r reduces
+//                                shard r in place, then every rank pulls the other shards.
+//   push  ga_push1_kernel        one-shot: STORE every gradient tile into every rank's staging slot
+//         ga_push_kernel         two-shot: scatter tiles to the shard owners, owner folds and stores
+//         ga_push_pipe_kernel    the result into every peer's gather region; the pipelined form
+//                                overlaps scatter / fold / unpack of consecutive rounds.
+//         (stores are posted and pack folds into the transfer; AUTO uses these across GPUs)
+//   local ga_hosted_direct_kernel  all ranks hosted in one process: no bucket, no flags.
 //
-// Nothing here is a contraction, so no tensor cores; the kernel is HBM-bound on one GPU and
-// NVLink-bound across GPUs.  Build: see __graft_entry__.build().
+// Cross-GPU ordering is by per-block flag rows written into the peers' memory (system-scope
+// fence + relaxed stores, one polling thread + one fence on the reader's side), with the flag epoch
+// kept in device memory so that a launch can be replayed from a CUDA graph.  Nothing here is a
+// contraction, so no tensor cores; the kernels are HBM-bound on one GPU and NVLink-bound across
+// GPUs.  Build: see __graft_entry__.build().
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -469,7 +478,7 @@ __device__ __forceinline__ void fold_tile(SrcFn src, float wf, int lane, OutFn o
     }
 }
 
-template <int W, int VARIANT, int OP>
+template <int W, int OP>
 __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_constant__ Params p) {
     __shared__ int s_abort;
     __shared__ int s_last;
@@ -483,7 +492,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     const uint32_t stride = gridDim.x * wpb;
     const uint32_t first = b * wpb + warp;
     const uint32_t T = p.total_tiles;
-    const uint32_t Ts = VARIANT == GA_VARIANT_ONESHOT_PUSH ? T : p.shard_tiles;   // tiles per staging slot
+    const uint32_t Ts = p.shard_tiles;            // tiles per staging slot
     const float wf = (float)W;
 
     Pad *mypad = p.pad[r];
@@ -505,20 +514,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     GA_TRACE(p, 1);
 
     // (1) scatter my gradient tiles into the owners' staging slots, nearest rank first
-    if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
-        for (uint32_t t = first; t < T; t += stride) {
-            const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
-            Vec v[kLaneVecs];
-            load_grad_tile(sg, t, lane, v);
-#pragma unroll
-            for (int jj = 0; jj < W; ++jj) {
-                const int j = (r + jj) % W;
-                Vec *dst = (Vec *)p.send[j] + ((size_t)r * Ts + t) * kTileVecs + lane;
-#pragma unroll
-                for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
-            }
-        }
-    } else {
+    {
         for (uint32_t i = first; i < Ts; i += stride) {
 #pragma unroll 1
             for (int jj = 0; jj < W; ++jj) {
@@ -543,14 +539,7 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
     if (!wait_flags<W>(mypad->ready[b], epoch, p, &s_abort)) return;
     GA_TRACE(p, 4);
 
-    if (VARIANT == GA_VARIANT_ONESHOT_PUSH) {
-        // (3) fold the W local slots of every tile straight into the gradient tensors
-        for (uint32_t t = first; t < T; t += stride) {
-            const Seg sg = sink.segs[find_seg(sink.segs, sink.n_seg, t)];
-            fold_tile<W, OP>([&](int s) { return mystage + ((size_t)s * Ts + t) * kTileVecs; }, wf, lane,
-                             [&](int u0, const Vec(&acc)[NB]) { store_grad_vecs<NB>(sg, t, lane, u0, acc); });
-        }
-    } else {
+    {
         // (3) fold my shard from the W local slots; result -> my gradients and every peer's gather region
         for (uint32_t i = first; i < Ts; i += stride) {
             const uint32_t t = r * Ts + i;
@@ -945,10 +934,10 @@ template <int W, int VARIANT> KernelFn pick_op(int op) {
            : op == GA_OP_F32_SUM ? (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_F32_SUM>
                                  : (KernelFn)ga_fused_kernel<W, VARIANT, GA_OP_F32_AVG>;
 }
-template <int W, int VARIANT> KernelFn pick_push_op(int op) {
-    return op == GA_OP_I32_SUM   ? (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_I32_SUM>
-           : op == GA_OP_F32_SUM ? (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_SUM>
-                                 : (KernelFn)ga_push_kernel<W, VARIANT, GA_OP_F32_AVG>;
+template <int W> KernelFn pick_push_op(int op) {
+    return op == GA_OP_I32_SUM   ? (KernelFn)ga_push_kernel<W, GA_OP_I32_SUM>
+           : op == GA_OP_F32_SUM ? (KernelFn)ga_push_kernel<W, GA_OP_F32_SUM>
+                                 : (KernelFn)ga_push_kernel<W, GA_OP_F32_AVG>;
 }
 template <int W> KernelFn pick_push1_op(int op) {
     return op == GA_OP_I32_SUM   ? (KernelFn)ga_push1_kernel<W, GA_OP_I32_SUM>
@@ -971,7 +960,7 @@ template <int W> KernelFn pick_variant(int variant, int op) {
         case GA_VARIANT_TWOSHOT_PIPE: return pick_pipe_op<W>(op);
         case GA_VARIANT_TWOSHOT: return pick_op<W, GA_VARIANT_TWOSHOT>(op);
         case GA_VARIANT_ONESHOT_PUSH: return pick_push1_op<W>(op);
-        case GA_VARIANT_TWOSHOT_PUSH: return pick_push_op<W, GA_VARIANT_TWOSHOT_PUSH>(op);
+        case GA_VARIANT_TWOSHOT_PUSH: return pick_push_op<W>(op);
     }
     return pick_op<W, GA_VARIANT_ONESHOT>(op);
 }
