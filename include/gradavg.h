@@ -19,6 +19,13 @@
  *     normal case is one process per GPU: n_local = 1 (`ga_create`).  `ga_create_local` hosts
  *     all `world` ranks on one device in one process (single launch, blockIdx.y = rank); it is
  *     the same kernels and flag protocol and is how the parity tests run on a one-GPU box.
+ *   - every entry point makes the context's device current while it runs and restores the caller's
+ *     device before returning.
+ *   - a launch carries no host-side counter (the flag epoch lives in device memory), so calls can be
+ *     captured in a CUDA graph and replayed, provided the pointer table fits the kernel parameters
+ *     (world-hosted ranks * n_tensors <= 128; larger tables are staged through a pinned ring, which
+ *     synchronises on reuse and therefore cannot be captured) and nothing has to be allocated
+ *     (create the context, and grow its bucket, before capture).
  *   - calls are collective: every rank calls the same function with the same sizes, in the
  *     same order.  Calls on one context must come from one thread at a time.
  *   - sums are taken in rank order, ((g0 + g1) + g2) + ..., each add one IEEE binary32

@@ -927,6 +927,24 @@ int fail(int code, const char *fmt, ...) {
             return fail(GA_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+// Makes `device` current for the duration of an entry point and puts the caller's device back on
+// the way out, so that a process driving several GPUs is not left on another device by a call.
+struct DeviceGuard {
+    int prev = -1;
+    cudaError_t err;
+    explicit DeviceGuard(int device) {
+        err = cudaGetDevice(&prev);
+        if (err == cudaSuccess && prev != device) err = cudaSetDevice(device);
+        else if (err != cudaSuccess) { prev = -1; err = cudaSetDevice(device); }
+        if (prev == device) prev = -1;          // nothing to restore
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define ENTER_DEVICE(dev)                                                                      \
+    DeviceGuard device_guard_(dev);                                                            \
+    if (device_guard_.err != cudaSuccess)                                                      \
+        return fail(GA_ECUDA, "cudaSetDevice(%d) failed: %s", (dev), cudaGetErrorString(device_guard_.err))
+
 typedef void (*KernelFn)(Params);
 
 template <int W, int VARIANT> KernelFn pick_op(int op) {
@@ -1029,7 +1047,7 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     int ndev = 0;
     CUDA_TRY(cudaGetDeviceCount(&ndev));
     if (device < 0 || device >= ndev) return fail(GA_EINVAL, "device=%d but %d CUDA devices visible", device, ndev);
-    CUDA_TRY(cudaSetDevice(device));
+    ENTER_DEVICE(device);
 
     ga_ctx *c = (ga_ctx *)calloc(1, sizeof(ga_ctx));
     if (!c) return fail(GA_EINVAL, "out of host memory");
@@ -1134,7 +1152,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     // One-shot push stages W copies of the set in every rank's bucket; beyond that, two-shot push.
     if (variant == GA_VARIANT_ONESHOT_PUSH && (size_t)total_tiles * kTileBytes * c->world > c->capacity_bytes)
         variant = GA_VARIANT_TWOSHOT_PUSH;
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     cudaStream_t st = (cudaStream_t)stream;
 
     Params p;
@@ -1268,7 +1286,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
 // that themselves, ga_average_host does it with its H2D copies).
 int drain_if_needed(ga_ctx *c, void *stream) {
     if (!c->last_was_tensor_call) return GA_OK;
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     ga_drain_kernel<<<1, kMaxWorld * kMaxWorld, 0, (cudaStream_t)stream>>>(
         c->own_pads_dev, c->n_local, c->world, c->timeout_ns, c->status_dev);
     CUDA_TRY(cudaGetLastError());
@@ -1347,7 +1365,7 @@ int ga_export_handle(ga_ctx *c, unsigned char out[GA_IPC_HANDLE_BYTES]) {
     if (!c || !out) return fail(GA_EINVAL, "NULL argument");
     if (c->n_local != 1) return fail(GA_ESTATE, "a local world has no handles to exchange");
     static_assert(sizeof(cudaIpcMemHandle_t) == GA_IPC_HANDLE_BYTES, "IPC handle size");
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     cudaIpcMemHandle_t h;
     CUDA_TRY(cudaIpcGetMemHandle(&h, c->base[0]));
     memcpy(out, &h, sizeof(h));
@@ -1358,7 +1376,7 @@ int ga_open_peers(ga_ctx *c, const unsigned char *handles) {
     if (!c) return fail(GA_EINVAL, "NULL context");
     if (c->opened) return c->n_local == c->world ? GA_OK : fail(GA_ESTATE, "peers already opened");
     if (!handles) return fail(GA_EINVAL, "NULL handles");
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     for (int r = 0; r < c->world; ++r) {
         if (r == c->rank_base) continue;
         cudaIpcMemHandle_t h;
@@ -1437,7 +1455,7 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
                     (unsigned long long)(total * kTileBytes), c->capacity_bytes);
     if (total == 0) return GA_OK;
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     cudaStream_t st = (cudaStream_t)stream;
     rc = drain_if_needed(c, stream);
     if (rc) return rc;
@@ -1541,11 +1559,11 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
         case GA_OPT_TRACE: {
             const size_t bytes = (size_t)kMaxBlocks * c->n_local * kTraceSlots * sizeof(unsigned long long);
             if (value && !c->trace_dev) {
-                CUDA_TRY(cudaSetDevice(c->device));
+                ENTER_DEVICE(c->device);
                 CUDA_TRY(cudaMalloc((void **)&c->trace_dev, bytes));
                 CUDA_TRY(cudaMemset(c->trace_dev, 0, bytes));
             } else if (!value && c->trace_dev) {
-                CUDA_TRY(cudaSetDevice(c->device));
+                ENTER_DEVICE(c->device);
                 CUDA_TRY(cudaDeviceSynchronize());
                 CUDA_TRY(cudaFree(c->trace_dev));
                 c->trace_dev = nullptr;
@@ -1565,7 +1583,7 @@ int ga_read_trace(ga_ctx *c, uint64_t *out, size_t max_words, int *blocks, int *
     if (!c->trace_dev) return fail(GA_ESTATE, "tracing is off (ga_set_option(ctx, GA_OPT_TRACE, 1))");
     const size_t words = (size_t)c->last_blocks * c->n_local * kTraceSlots;
     if (words > max_words) return fail(GA_ECAPACITY, "trace needs %zu words, buffer has %zu", words, max_words);
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     CUDA_TRY(cudaDeviceSynchronize());
     CUDA_TRY(cudaMemcpy(out, c->trace_dev, words * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     if (blocks) *blocks = c->last_blocks;
@@ -1585,7 +1603,7 @@ int ga_status(ga_ctx *c) {
 
 int ga_close_peers(ga_ctx *c) {
     if (!c) return GA_OK;
-    CUDA_TRY(cudaSetDevice(c->device));
+    ENTER_DEVICE(c->device);
     CUDA_TRY(cudaDeviceSynchronize());
     for (int r = 0; r < c->world; ++r) {
         if (c->peer_base[r]) {
@@ -1602,7 +1620,7 @@ int ga_close_peers(ga_ctx *c) {
 
 int ga_destroy(ga_ctx *c) {
     if (!c) return GA_OK;
-    cudaSetDevice(c->device);
+    DeviceGuard device_guard_(c->device);
     cudaDeviceSynchronize();
     for (int r = 0; r < c->world; ++r)
         if (c->peer_base[r]) cudaIpcCloseMemHandle(c->peer_base[r]);
@@ -1682,7 +1700,7 @@ extern "C" int ga_average_static(int world, int device, const void *const *grad_
         variant = (world <= 2 || total * kTileBytes <= ((size_t)512 << 10)) ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     if (variant != GA_VARIANT_ONESHOT && variant != GA_VARIANT_TWOSHOT) return fail(GA_EINVAL, "unknown variant %d", variant);
 
-    CUDA_TRY(cudaSetDevice(device));
+    ENTER_DEVICE(device);
     StaticDevice &sd = g_static_dev[device];
     if (!sd.ready) {
         // Once per device, with that device current: resolve the array's address ON THIS DEVICE.

@@ -84,3 +84,36 @@ def test_reference_style_script_two_ranks(tmp_path):
         losses[mode] = [[l for l in o.splitlines() if l.startswith("final loss")][0] for o in outs]
         assert all("done" in o for o in outs)
     assert losses["fused"] == losses["per-tensor"]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_entry_points_restore_the_callers_device(built):
+    """A process driving several GPUs: a context on cuda:0 used while cuda:1 is current works and
+    leaves cuda:1 current (every entry point switches to its device and back)."""
+    import ctypes
+    import oracle
+    lib = built
+    torch.cuda.set_device(1)
+    world = 2
+    ctx = ctypes.c_void_p()
+    assert lib.ga_create_local(world, 0, 1 << 20, ctypes.byref(ctx)) == 0, lib.ga_last_error()
+    try:
+        assert torch.cuda.current_device() == 1
+        host = [[g.numpy() for g in oracle.seeded_grads(oracle.MINI_SHAPES, r)] for r in range(world)]
+        want = [oracle.fold_average_c([host[r][i] for r in range(world)]) for i in range(len(oracle.MINI_SHAPES))]
+        dev = [[torch.from_numpy(a).to("cuda:0") for a in rank] for rank in host]
+        n = len(dev[0])
+        ptrs = (ctypes.c_void_p * (n * world))(*[t.data_ptr() for ts in dev for t in ts])
+        numel = (ctypes.c_int64 * n)(*[t.numel() for t in dev[0]])
+        st = ctypes.c_void_p(torch.cuda.current_stream(torch.device("cuda", 0)).cuda_stream)
+        for variant in (1, 2, 6):
+            assert lib.ga_average(ctx, ptrs, numel, n, st, variant) == 0, lib.ga_last_error()
+            x = torch.ones(4, device="cuda")                   # allocated on the CURRENT device
+            assert x.device.index == 1 and torch.cuda.current_device() == 1
+        torch.cuda.synchronize(0)
+        del want                                               # three averages in a row: the values are covered elsewhere
+        assert lib.ga_status(ctx) == 0
+    finally:
+        lib.ga_destroy(ctx)
+        assert torch.cuda.current_device() == 1
+        torch.cuda.set_device(0)
