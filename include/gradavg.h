@@ -171,6 +171,10 @@ size_t ga_capacity(const ga_ctx *ctx);
 /* What AUTO resolves to for `nbytes` (GA_VARIANT_ONESHOT or GA_VARIANT_TWOSHOT). */
 int ga_pick_variant(const ga_ctx *ctx, size_t nbytes);
 
+/* The same rule without a context (pure host arithmetic, no GPU needed): what AUTO would pick for a
+ * job of `world` ranks of which `n_local` are hosted per process, with `capacity_bytes` buckets. */
+int ga_auto_variant(int world, int n_local, size_t capacity_bytes, size_t nbytes);
+
 /* Kernels launched by this context so far (for bench.py's gpu_launches). */
 uint64_t ga_launch_count(const ga_ctx *ctx);
 

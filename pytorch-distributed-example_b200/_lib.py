@@ -41,6 +41,7 @@ SIGNATURES = {
     "ga_n_local": (_c.c_int, [_c.c_void_p]),
     "ga_capacity": (_c.c_size_t, [_c.c_void_p]),
     "ga_pick_variant": (_c.c_int, [_c.c_void_p, _c.c_size_t]),
+    "ga_auto_variant": (_c.c_int, [_c.c_int, _c.c_int, _c.c_size_t, _c.c_size_t]),
     "ga_launch_count": (_c.c_uint64, [_c.c_void_p]),
     "ga_last_grid": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_int), _c.POINTER(_c.c_int)]),
     "ga_set_option": (_c.c_int, [_c.c_void_p, _c.c_int, _c.c_int64]),

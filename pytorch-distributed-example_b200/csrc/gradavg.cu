@@ -1037,6 +1037,18 @@ namespace {
 
 size_t tiles_for_elems(int64_t numel) { return (size_t)((numel + kTileElems - 1) / kTileElems); }
 
+// AUTO thresholds, from the round-1 sweeps (profiles/): hosted worlds move everything through HBM
+// and prefer the pull kernels; across GPUs the push kernels win at every size, one-shot while its
+// (world-1)*S egress stays below ~8 MiB.
+void set_auto_thresholds(ga_ctx *c) {
+    const int world = c->world, n_local = c->n_local;
+    if (world <= 2) c->oneshot_max_bytes = (size_t)32 << 20;   // same link bytes either way; two-shot stages less (r01m sweep)
+    else if (n_local > 1) c->oneshot_max_bytes = (size_t)512 << 10;
+    else c->oneshot_max_bytes = ((size_t)8 << 20) / (size_t)(world - 1);
+    c->pipe_min_bytes = (size_t)32 << 20;
+    c->pipe_max_bytes = (size_t)128 << 20;
+}
+
 int create_common(int rank_base, int n_local, int world, int device, size_t capacity_bytes, ga_ctx **out) {
     if (!out) return fail(GA_EINVAL, "out is NULL");
     *out = nullptr;
@@ -1055,14 +1067,7 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->capacity_bytes = (capacity_bytes + kTileBytes - 1) / kTileBytes * kTileBytes;
     if (c->capacity_bytes / kTileBytes > 0xffffffffull) { free(c); return fail(GA_ECAPACITY, "capacity too large"); }
     c->region_bytes = c->capacity_bytes + (size_t)kMaxWorld * kTileBytes;
-    // AUTO thresholds, from the round-1 sweeps (profiles/): hosted worlds move everything through
-    // HBM and prefer the pull kernels; across GPUs the push kernels win at every size, one-shot
-    // while its (world-1)*S egress stays below ~8 MiB.
-    if (world <= 2) c->oneshot_max_bytes = (size_t)32 << 20;   // same link bytes either way; two-shot stages less (r01m sweep)
-    else if (n_local > 1) c->oneshot_max_bytes = (size_t)512 << 10;
-    else c->oneshot_max_bytes = ((size_t)8 << 20) / (size_t)(world - 1);
-    c->pipe_min_bytes = (size_t)32 << 20;
-    c->pipe_max_bytes = (size_t)128 << 20;
+    set_auto_thresholds(c);
     c->timeout_ns = 30ull * 1000000000ull;
     c->host_chunk_bytes = (size_t)8 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
@@ -1539,6 +1544,15 @@ int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
     if (c->n_local > 1 || c->world == 1) return one_shot ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     if (one_shot && nbytes * c->world <= c->capacity_bytes) return GA_VARIANT_ONESHOT_PUSH;
     return nbytes <= c->pipe_max_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
+}
+
+int ga_auto_variant(int world, int n_local, size_t capacity_bytes, size_t nbytes) {
+    if (world < 1 || world > kMaxWorld || n_local < 1 || n_local > world) return fail(GA_EINVAL, "bad world / n_local");
+    ga_ctx c;
+    memset(&c, 0, sizeof(c));
+    c.world = world; c.n_local = n_local; c.capacity_bytes = capacity_bytes;
+    set_auto_thresholds(&c);
+    return ga_pick_variant(&c, nbytes);
 }
 
 uint64_t ga_launch_count(const ga_ctx *c) { return c ? c->launches : 0; }

@@ -92,3 +92,26 @@ def test_product_never_touches_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
                 assert "liboracle" not in text, f
+
+
+def test_auto_variant_rules(built):
+    """AUTO as a pure host function: the thresholds fitted from the round-1 sweeps."""
+    ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT = 1, 2, 3, 4, 5, 6
+    MiB = 1 << 20
+    f = built.ga_auto_variant
+    # one rank per GPU, 8 ranks: one-shot push while (world-1)*S <= 8 MiB, pipelined up to 128 MiB, then plain push
+    assert f(8, 1, 64 * MiB, 4096) == ONESHOT_PUSH
+    assert f(8, 1, 64 * MiB, MiB) == ONESHOT_PUSH
+    assert f(8, 1, 64 * MiB, 1724320) == TWOSHOT_PIPE
+    assert f(8, 1, 64 * MiB, 64 * MiB) == TWOSHOT_PIPE
+    assert f(8, 1, 1024 * MiB, 256 * MiB) == TWOSHOT_PUSH
+    # one-shot push needs world * S of staging: without it, two-shot
+    assert f(8, 1, 4 * MiB, MiB) == TWOSHOT_PIPE
+    # two ranks: one-shot up to 32 MiB
+    assert f(2, 1, 1024 * MiB, 16 * MiB) == ONESHOT_PUSH
+    assert f(2, 1, 1024 * MiB, 64 * MiB) == TWOSHOT_PIPE
+    # every rank hosted in one process: no exchange at all; a hosted sub-world uses the pull kernels
+    assert f(4, 4, 64 * MiB, 64 * MiB) == HOSTED_DIRECT
+    assert f(4, 2, 64 * MiB, 64 * MiB) == TWOSHOT and f(4, 2, 64 * MiB, 4096) == ONESHOT
+    assert f(1, 1, 64 * MiB, MiB) == ONESHOT
+    assert f(9, 1, MiB, 4) == -1 and f(2, 3, MiB, 4) == -1
