@@ -30,6 +30,15 @@ class Rank:
         self.gather = {}
         self.grads = {}
 
+    def store(self, layout, key, value):
+        """A store into the bucket region.  The pull bucket, the two-shot staging slots and the two
+        one-shot halves are different LAYOUTS of the same memory: a store in one layout destroys
+        whatever another layout kept there (conservatively: all of it), except that the two one-shot
+        halves do not overlap each other."""
+        for k in [k for k in self.send if k[0] != layout and not (k[0] in ("h0", "h1") and layout in ("h0", "h1"))]:
+            del self.send[k]
+        self.send[(layout,) + key] = value
+
 
 class World:
     def __init__(self, world, blocks, seed):
@@ -66,23 +75,23 @@ class World:
                 [j * Ts + i for i in range(Ts) if i % B == b for j in range(W) if j * Ts + i < T]
             for t in tiles:                                                 # (1) pack
                 expect(me.grads[t], mine(t), "pack")
-                me.send[t] = mine(t)
+                me.store("pull", (t,), mine(t))
                 yield "ok"
             yield from raise_flags("ready", epoch)
             yield from wait(me.ready[b], epoch)
             if variant == ONESHOT:
                 for t in tiles:                                             # (3) reduce everything
                     for s in range(W):
-                        expect(self.ranks[s].send.get(t), ("in", call, s, t), "one-shot pull")
+                        expect(self.ranks[s].send.get(("pull", t)), ("in", call, s, t), "one-shot pull")
                         yield "ok"
                     me.grads[t] = fold + (t,)
             else:
                 own = [r * Ts + i for i in range(Ts) if i % B == b and r * Ts + i < T]
                 for t in own:                                               # (3) reduce-scatter, in place
                     for s in range(W):
-                        expect(self.ranks[s].send.get(t), ("in", call, s, t), "two-shot pull reduce")
+                        expect(self.ranks[s].send.get(("pull", t)), ("in", call, s, t), "two-shot pull reduce")
                         yield "ok"
-                    me.send[t] = fold + (t,)
+                    me.store("pull", (t,), fold + (t,))
                     me.grads[t] = fold + (t,)
                 yield from raise_flags("mid", epoch)
                 yield from wait(me.mid[b], epoch)
@@ -94,7 +103,7 @@ class World:
                         t = j * Ts + i
                         if t >= T:
                             continue
-                        expect(self.ranks[j].send.get(t), fold + (t,), "two-shot pull gather")
+                        expect(self.ranks[j].send.get(("pull", t)), fold + (t,), "two-shot pull gather")
                         me.grads[t] = fold + (t,)
                         yield "ok"
             last_kind, last_epoch = 0, epoch
@@ -108,13 +117,13 @@ class World:
                 expect(me.grads[t], mine(t), "scatter source")
                 for jj in range(W):
                     j = (r + jj) % W
-                    self.ranks[j].send[(half, r, t)] = mine(t)
+                    self.ranks[j].store("h%d" % half, (r, t), mine(t))
                     yield "ok"
             yield from raise_flags("ready", epoch)
             yield from wait(me.ready[b], epoch)
             for t in tiles:
                 for s in range(W):
-                    expect(me.send.get((half, s, t)), ("in", call, s, t), "one-shot push fold")
+                    expect(me.send.get(("h%d" % half, s, t)), ("in", call, s, t), "one-shot push fold")
                     yield "ok"
                 me.grads[t] = fold + (t,)
             last_kind, last_epoch = (1 if dbuf else 0), epoch
@@ -134,7 +143,7 @@ class World:
                         if t >= T:
                             continue
                         expect(me.grads[t], mine(t), "scatter source")
-                        self.ranks[j].send[(r, i)] = mine(t)
+                        self.ranks[j].store("stage", (r, i), mine(t))
                         yield "ok"
 
             def fold_round(q):
@@ -143,7 +152,7 @@ class World:
                     if t >= T:
                         continue
                     for s in range(W):
-                        expect(me.send.get((s, i)), ("in", call, s, t), "two-shot push fold")
+                        expect(me.send.get(("stage", s, i)), ("in", call, s, t), "two-shot push fold")
                         yield "ok"
                     me.grads[t] = fold + (t,)
                     for jj in range(1, W):
