@@ -117,3 +117,31 @@ def test_entry_points_restore_the_callers_device(built):
         lib.ga_destroy(ctx)
         assert torch.cuda.current_device() == 1
         torch.cuda.set_device(0)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_toy_example_prints_the_reference_lines(golden_dir):
+    """examples/toy_main.py on 2 GPUs (int32 SUM through the fused kernel) prints, line for line,
+    what the REAL reference toy/main.py printed on gloo with the same seeds (tests/golden/toy.json)."""
+    import json
+    import os
+    import subprocess
+    import sys
+    from oracle.gloo_path import free_port
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    want = json.load(open(os.path.join(golden_dir, "toy.json")))["worlds"]["2"]
+    port = free_port()
+    procs = [subprocess.Popen([sys.executable, os.path.join(root, "examples", "toy_main.py"), "-s", "2", "-r", str(r),
+                               "--steps", "3", "--pause", "0", "--seed", "100", "-i", "tcp://127.0.0.1:%d" % port],
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                              env=dict(os.environ, GA_TIMEOUT_MS="8000")) for r in range(2)]
+    for r, p in enumerate(procs):
+        try:
+            out, err = p.communicate(timeout=200)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        assert p.returncode == 0, err[-1500:]
+        got = "".join(l + "\n" for l in out.splitlines() if l.startswith("rank:"))
+        assert got == want[r]
