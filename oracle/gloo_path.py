@@ -14,7 +14,6 @@ import os
 import socket
 import time
 
-import numpy as np
 import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp

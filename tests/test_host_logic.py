@@ -170,3 +170,21 @@ def test_plan_cache_survives_id_reuse():
             avg.average_gradients(ps)
     finally:
         averager.torch.cuda.current_stream = orig
+
+
+def test_init_process_group_selects_the_ranks_gpu(monkeypatch):
+    """the reference never selects a device, so every rank would sit on GPU 0; the
+    stand-in picks LOCAL_RANK (torchrun) or the rank, modulo the visible devices, before the
+    rendezvous, and forwards the reference's arguments unchanged."""
+    chosen, forwarded = [], {}
+    monkeypatch.setattr(torch.cuda, "is_available", lambda: True)
+    monkeypatch.setattr(torch.cuda, "device_count", lambda: 4)
+    monkeypatch.setattr(torch.cuda, "set_device", lambda d: chosen.append(d))
+    monkeypatch.setattr(distributed._td, "init_process_group", lambda **kw: forwarded.update(kw))
+    monkeypatch.delenv("LOCAL_RANK", raising=False)
+    distributed.init_process_group(backend="nccl", init_method="tcp://127.0.0.1:23456", rank=6, world_size=8)
+    assert chosen == [2]                                     # 6 % 4
+    assert forwarded == {"backend": "nccl", "init_method": "tcp://127.0.0.1:23456", "rank": 6, "world_size": 8}
+    monkeypatch.setenv("LOCAL_RANK", "3")
+    distributed.init_process_group(backend="gloo", rank=11, world_size=16)
+    assert chosen[-1] == 3

@@ -1,4 +1,4 @@
-import sys, time, json
+import sys, time
 import os; sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import pytorch_distributed_example_b200 as ga
