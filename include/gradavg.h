@@ -228,6 +228,10 @@ int ga_status(ga_ctx *ctx);
 int ga_average_static(int world, int device, const void *const *grad_ptrs, const int64_t *numel,
                       int n_tensors, void *stream, int variant);
 
+/* Waits for everything enqueued on `stream` (for hosts without a CUDA runtime of their own, e.g. a
+ * plain C program using ga_average_host), then returns ga_status(). */
+int ga_synchronize(ga_ctx *ctx, void *stream);
+
 /*
  * Tear-down is two collective steps, because an exporter must not free memory that a peer still
  * has mapped: every rank calls ga_close_peers (unmaps the peers' buckets; the context can no longer

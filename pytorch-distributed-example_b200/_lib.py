@@ -48,6 +48,7 @@ SIGNATURES = {
     "ga_read_trace": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_uint64), _c.c_size_t, _c.POINTER(_c.c_int),
                                  _c.POINTER(_c.c_int)]),
     "ga_status": (_c.c_int, [_c.c_void_p]),
+    "ga_synchronize": (_c.c_int, [_c.c_void_p, _c.c_void_p]),
     "ga_average_static": (_c.c_int, [_c.c_int, _c.c_int, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
                                      _c.c_void_p, _c.c_int]),
     "ga_close_peers": (_c.c_int, [_c.c_void_p]),

@@ -1356,6 +1356,8 @@ int build_layout(const int64_t *numel, int n_tensors, uint64_t *total_tiles) {
 // ------------------------------------------------------------------------------------------
 extern "C" {
 
+int ga_status(ga_ctx *c);
+
 const char *ga_last_error(void) { return g_err; }
 
 int ga_create(int rank, int world, int device, size_t capacity_bytes, ga_ctx **out) {
@@ -1590,6 +1592,13 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
         case GA_OPT_PIPE_GROUP: c->pipe_group_opt = value < 0 ? 0 : (value > 64 ? 64 : (int)value); return GA_OK;
     }
     return fail(GA_EINVAL, "unknown option %d", option);
+}
+
+int ga_synchronize(ga_ctx *c, void *stream) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    ENTER_DEVICE(c->device);
+    CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    return ga_status(c);
 }
 
 int ga_read_trace(ga_ctx *c, uint64_t *out, size_t max_words, int *blocks, int *slots) {
