@@ -28,6 +28,13 @@
  *     (create the context, and grow its bucket, before capture).
  *   - calls are collective: every rank calls the same function with the same sizes, in the
  *     same order.  Calls on one context must come from one thread at a time.
+ *   - launches of one context must be ORDERED with respect to each other on the GPU: the flag epoch,
+ *     the staging regions and the bucket belong to the context, so two of its kernels running at
+ *     once would share them and give wrong gradients.  Calls on one stream are ordered.  When a call
+ *     arrives on a different stream than the previous one, the library makes the new stream wait for
+ *     the previous launch (one event record + wait) -- except while either stream is being captured,
+ *     where the caller's own graph edges must provide the order.  Use one context per concurrent
+ *     stream if launches are meant to overlap.
  *   - sums are taken in rank order, ((g0 + g1) + g2) + ..., each add one IEEE binary32
  *     operation, then ONE IEEE division by (float)world.  Results are therefore identical on
  *     every rank and bit-identical to oracle/fold.c.
@@ -64,6 +71,13 @@ extern "C" {
                                      each tile is read from all ranks, folded and written back: 2*W*S bytes, no bucket */
 #define GA_VARIANT_TWOSHOT_PIPE 5 /* two-shot push, software-pipelined in rounds: scatter of round q+1 and
                                      unpack of round q-1 overlap the fold of round q (large tensor calls)   */
+#define GA_VARIANT_VIEW     7   /* ga_average_view only: in place on the view region, scatter blocks and fold blocks
+                                     running at once with one flag per chunk; bit-exact like every variant above */
+#define GA_VARIANT_NVLS     8   /* ga_average_view only, OPT-IN, one rank per GPU with NVSwitch multicast: the switch
+                                     adds the replicas (multimem.ld_reduce) and replicates the result (multimem.st).
+                                     Half the link bytes.  NOT the rank-order sum: the switch returns the correctly
+                                     rounded exact sum of the `world` values, so results can differ from every other
+                                     variant in the last bit (oracle: oracle/fold.c fold_exact_*); never picked by AUTO */
 
 /* element type + operation */
 #define GA_OP_F32_AVG   0   /* fp32: rank-order sum, then / (float)world      mnist/main.py:126-127 */
@@ -77,6 +91,12 @@ extern "C" {
 #define GA_OPT_TRACE             6   /* 1: the push kernels record per-block phase timestamps (globaltimer ns) */
 #define GA_OPT_HOST_CHUNK_BYTES  5   /* ga_average_host: largest chunk of the copy-in / reduce / copy-out pipeline */
 #define GA_OPT_PIPE_GROUP        4   /* TWOSHOT_PIPE: tile slots per block per round (0 = automatic) */
+#define GA_OPT_VIEW_CHUNK_TILES  7   /* GA_VARIANT_VIEW: 2 KiB tiles per chunk (0 = automatic) */
+
+/* flags for ga_view_create */
+#define GA_VIEW_MULTICAST        1   /* also map the regions through an NVSwitch multicast object when the GPUs
+                                        support it (one rank per GPU only); enables GA_VARIANT_NVLS */
+#define GA_VIEW_HANDLE_BYTES   128   /* what ga_view_export writes per rank */
 
 typedef struct ga_ctx ga_ctx;
 
@@ -128,6 +148,22 @@ int ga_average(ga_ctx *ctx, const void *const *grad_ptrs, const int64_t *numel, 
 int ga_allreduce_tensors(ga_ctx *ctx, const void *const *ptrs, const int64_t *numel, int n_tensors,
                          int op, void *stream, int variant);
 
+/* Same with a per-call cap on thread blocks per rank (0 = none): what the overlap mode uses for a
+ * bucket that is averaged while loss.backward() (mnist/main.py:92) still runs, so that the remaining
+ * backward kernels keep their SMs -- without touching the context's GA_OPT_MAX_BLOCKS. */
+int ga_allreduce_tensors_ex(ga_ctx *ctx, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                            int op, void *stream, int variant, int max_blocks);
+
+/*
+ * Replicates rank `root`'s tensors into the same-shaped tensors of every other rank (32-bit
+ * elements, any type).  The reference builds Net() on every rank and relies on identical initial
+ * parameters that it never arranges (no seed, no broadcast: mnist/main.py:185); this is the missing
+ * step, over the peer mappings and flag protocol already in place: the root stores its tensors
+ * straight into every peer's gather region, the peers unpack.  One kernel on `stream`; collective.
+ */
+int ga_broadcast_tensors(ga_ctx *ctx, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                         int root, void *stream);
+
 /*
  * Bucket-direct form, for the size sweep and the same-buffer comparison with NCCL: the caller
  * has written `nbytes` into ga_send_ptr() (stream-ordered before this call); the averaged
@@ -146,6 +182,52 @@ int ga_allreduce_bucket(ga_ctx *ctx, size_t nbytes, int op, void *stream, int va
  */
 int ga_average_host(ga_ctx *ctx, void *const *host_ptrs, const int64_t *numel, int n_tensors,
                     void *stream, int variant);
+
+/*
+ * Gradients as views.  The steps either side of the hot path only touch p.grad:
+ * zero_grad() + backward() write it (mnist/main.py:91-92), optimizer.step() reads it (:96).  If every
+ * p.grad IS a slice of one flat region that the peers have mapped, averaging (:122-127) needs neither
+ * pack nor unpack: ga_average_view works in place on that region.
+ *
+ *   ga_view_create   allocates `nbytes` (<= the context's capacity: the bucket serves as staging) per
+ *                    hosted rank.  With GA_VIEW_MULTICAST, on a one-rank-per-GPU world whose GPUs report
+ *                    CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, the region is a cuMem allocation that is
+ *                    also bound to an NVSwitch multicast object; otherwise a plain cudaMalloc shared
+ *                    through CUDA-IPC like the bucket.  Collective: same arguments on every rank.
+ *   ga_view_export   GA_VIEW_HANDLE_BYTES to all-gather over the script's own process group
+ *                    (mnist/main.py:199-203), like ga_export_handle.
+ *   ga_view_open     maps every peer's region (and joins the multicast object).  `handles` = world *
+ *                    GA_VIEW_HANDLE_BYTES in rank order.  For the cuMem kind the descriptors are fetched
+ *                    from the exporting processes with pidfd_getfd (same user, Linux >= 5.6), so every
+ *                    exporter must still be alive and must not have called ga_view_bind yet.
+ *   -- barrier --
+ *   ga_view_bind     binds this rank's memory to the multicast object and maps it (a no-op for the
+ *                    CUDA-IPC kind).  Barrier again before the first ga_average_view.
+ *   ga_view_ptr      device pointer of hosted rank `local_rank`'s region: lay the gradients out in it
+ *                    with ga_bucket_offset (2 KiB-aligned tensors) or any layout every rank shares --
+ *                    the kernels treat it as one flat array.
+ * A local world (ga_create_local) needs only ga_view_create.  The regions are unmapped by
+ * ga_close_peers and freed by ga_destroy.
+ */
+int ga_view_create(ga_ctx *ctx, size_t nbytes, int flags);
+int ga_view_export(ga_ctx *ctx, unsigned char out[GA_VIEW_HANDLE_BYTES]);
+int ga_view_open(ga_ctx *ctx, const unsigned char *handles);
+int ga_view_bind(ga_ctx *ctx);
+void *ga_view_ptr(ga_ctx *ctx, int local_rank);
+size_t ga_view_bytes(const ga_ctx *ctx);
+int ga_view_has_multicast(const ga_ctx *ctx);
+
+/* 1 if `device` supports NVSwitch multicast objects with POSIX descriptors (what GA_VIEW_MULTICAST needs). */
+int ga_multicast_supported(int device);
+
+/*
+ * Trainer.average_gradients (mnist/main.py:122-127) IN PLACE on the first `nbytes` of every rank's
+ * view region: afterwards every rank's region holds the rank-order sum divided by (float)world
+ * (GA_OP_F32_AVG; the other ops as in ga_allreduce_tensors).  One kernel on `stream`, asynchronous.
+ * variant: GA_VARIANT_AUTO / GA_VARIANT_VIEW (bit-exact) or GA_VARIANT_NVLS (opt-in, see above).
+ * This is also the same-buffer form to time against NCCL all_reduce, which is in place too.
+ */
+int ga_average_view(ga_ctx *ctx, size_t nbytes, int op, void *stream, int variant);
 
 /*
  * Call on `stream` before writing into ga_send_ptr() if the previous call on this context was a
@@ -215,18 +297,34 @@ int ga_status(ga_ctx *ctx);
  *
  * Limits: world * (bucket bytes of the set, each tensor padded to 2 KiB) <= 8 MiB, and
  * world * n_tensors <= 128 pointers; beyond either it returns GA_ECAPACITY and launches nothing.
- * The 8.6 MB array is resident on every GPU that loads the library, until the process exits.
+ * The array is 8 945 664 bytes (8.53 MiB: 8 MiB of bucket + 8 flag pads) and stays resident on
+ * every GPU that has used the library, until the process exits.
  *
  * First call on a device: resolves the array's address on that device (cudaGetSymbolAddress, with
- * the device made current) and caches it.  Make that first call before starting any stream capture.
+ * the device made current) and caches it.  With CUDA's default lazy module loading that is also the
+ * moment the driver loads the library's device code and reserves the array on that GPU -- the one
+ * device-memory reservation this entry point ever causes.  So make that first call (or
+ * ga_static_status) at start-up: before any stream capture, before the no-allocation region begins
+ * and before the host application's pool claims the rest of the memory; or run with
+ * CUDA_MODULE_LOADING=EAGER, which moves the reservation to context creation.
  *
  * All calls on one device share the one array.  It keeps whatever the previous call left, so each
- * call first clears, on `stream`, the words its flag protocol counts up from zero.  Two calls whose
- * GPU work can overlap (different streams without an event between them, or two host threads)
- * race on that array and give wrong gradients; order them yourself.
+ * call first clears, on `stream`, the words its flag protocol counts up from zero (three small
+ * strided memsets).  Two calls whose GPU work can overlap (different streams without an event
+ * between them, or two host threads) race on that array and give wrong gradients; order them
+ * yourself.
+ *
+ * Errors inside the kernel: a flag wait that expires (GA_TIMEOUT_MS in the environment, default 30 s)
+ * makes the blocks leave early with the gradients partly averaged.  The call itself has long returned
+ * GA_OK by then; ga_static_status reports it.
  */
 int ga_average_static(int world, int device, const void *const *grad_ptrs, const int64_t *numel,
                       int n_tensors, void *stream, int variant);
+
+/* Waits for `stream`, then reads the status word the ga_average_static kernels leave in the array
+ * (a 4-byte copy into a stack variable: no allocation here either).  GA_OK, or GA_ETIMEOUT if a kernel
+ * of the last call gave up on a flag.  No counterpart in the reference. */
+int ga_static_status(int device, void *stream);
 
 /* Waits for everything enqueued on `stream` (for hosts without a CUDA runtime of their own, e.g. a
  * plain C program using ga_average_host), then returns ga_status(). */

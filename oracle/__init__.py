@@ -12,7 +12,9 @@ typo patched in memory), runs its own `Trainer.average_gradients` 
 on gloo and stores inputs + outputs under `tests/golden/`; `tests/test_oracle.py` checks
 every function of this package against those files.
 """
-from .host_fold import fold_average, fold_average_c, fold_sum_i32, fold_sum_i32_c, build_c_oracle  # noqa: F401
+from .host_fold import (  # noqa: F401
+    fold_average, fold_average_c, fold_sum_i32, fold_sum_i32_c, build_c_oracle, fold_wide_average, fold_wide_average_c,
+)
 from .gradient_sets import (  # noqa: F401
     MNIST_CNN_SHAPES, MINI_SHAPES, resnet18_shapes, seeded_grads, seeded_positive_grads, numel_of,
 )

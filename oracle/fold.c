@@ -40,3 +40,24 @@ void oracle_fold_sum_i32(const int32_t *const *g, int world, size_t n, int32_t *
         out[i] = (int32_t)acc;
     }
 }
+
+/*
+ * Oracle of the OPT-IN in-switch variant only (GA_VARIANT_NVLS): the NVSwitch adds the `world`
+ * replicas in a wide accumulator and rounds once (measured on this pool: 65 536 of 65 536 results
+ * equal the correctly rounded exact sum, profiles/r02_nvlink_probe.md), then the kernel divides by
+ * (float)world as mnist/main.py:127 does.  Restated as a binary64 sum rounded to binary32: exact
+ * whenever the addends' exponents lie within 29 binades of each other, which holds for gradient
+ * data; it is NOT the rank-order fold above and not what the reference's gloo ring computes either
+ * (both differ from it in the last bit on about half of the elements).
+ */
+void oracle_fold_wide_average_f32(const float *const *g, int world, size_t n, float *out, int divide)
+{
+    const float w = (float)world;
+    for (size_t i = 0; i < n; ++i) {
+        double acc = (double)g[0][i];
+        for (int r = 1; r < world; ++r)
+            acc += (double)g[r][i];
+        const float s = (float)acc;
+        out[i] = divide ? s / w : s;
+    }
+}

@@ -36,6 +36,9 @@ def _c():
         _lib.oracle_fold_sum_i32.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int,
                                              ctypes.c_size_t, ctypes.c_void_p]
         _lib.oracle_fold_sum_i32.restype = None
+        _lib.oracle_fold_wide_average_f32.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int,
+                                                      ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int]
+        _lib.oracle_fold_wide_average_f32.restype = None
     return _lib
 
 
@@ -73,4 +76,22 @@ def fold_sum_i32_c(per_rank):
     arrs = [np.ascontiguousarray(a, dtype=np.int32) for a in per_rank]
     out = np.empty_like(arrs[0])
     _c().oracle_fold_sum_i32(_ptr_array(arrs), len(arrs), arrs[0].size, out.ctypes.data)
+    return out
+
+
+def fold_wide_average(per_rank, divide=True):
+    """numpy oracle of the opt-in NVSwitch variant: binary64 sum over the ranks rounded once to
+    binary32, then the binary32 division of mnist/main.py:127 (see fold.c)."""
+    arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in per_rank]
+    acc = arrs[0].astype(np.float64)
+    for a in arrs[1:]:
+        acc = acc + a.astype(np.float64)
+    s = acc.astype(np.float32)
+    return s / np.float32(float(len(arrs))) if divide else s
+
+
+def fold_wide_average_c(per_rank, divide=True):
+    arrs = [np.ascontiguousarray(a, dtype=np.float32) for a in per_rank]
+    out = np.empty_like(arrs[0])
+    _c().oracle_fold_wide_average_f32(_ptr_array(arrs), len(arrs), arrs[0].size, out.ctypes.data, 1 if divide else 0)
     return out

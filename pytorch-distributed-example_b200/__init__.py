@@ -17,10 +17,10 @@ from . import distributed  # noqa: F401
 from ._lib import GradAvgError, lib_path, load_library  # noqa: F401
 from .averager import (  # noqa: F401
     GradAverager, average_gradients, default_averager, reset_default_averager,
-    ONESHOT, TWOSHOT, AUTO, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT,
+    ONESHOT, TWOSHOT, AUTO, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT, VIEW, NVLS,
 )
 from .trainer import install  # noqa: F401
 from .overlap import OverlappedAverager, plan_buckets  # noqa: F401
 
 __all__ = ["distributed", "GradAverager", "GradAvgError", "average_gradients", "default_averager",
-           "reset_default_averager", "install", "OverlappedAverager", "plan_buckets", "load_library", "lib_path", "ONESHOT", "TWOSHOT", "AUTO", "ONESHOT_PUSH", "TWOSHOT_PUSH", "TWOSHOT_PIPE", "HOSTED_DIRECT"]
+           "reset_default_averager", "install", "OverlappedAverager", "plan_buckets", "load_library", "lib_path", "ONESHOT", "TWOSHOT", "AUTO", "ONESHOT_PUSH", "TWOSHOT_PUSH", "TWOSHOT_PIPE", "HOSTED_DIRECT", "VIEW", "NVLS"]

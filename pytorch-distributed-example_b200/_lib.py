@@ -9,10 +9,14 @@ GA_OK, GA_EINVAL, GA_ECUDA, GA_ECAPACITY, GA_ESTATE, GA_ETIMEOUT = 0, -1, -2, -3
 VARIANT_AUTO, VARIANT_ONESHOT, VARIANT_TWOSHOT = 0, 1, 2
 VARIANT_ONESHOT_PUSH, VARIANT_TWOSHOT_PUSH, VARIANT_TWOSHOT_PIPE = 3, 4, 5
 VARIANT_HOSTED_DIRECT = 6
+VARIANT_VIEW, VARIANT_NVLS = 7, 8
 OP_F32_AVG, OP_I32_SUM, OP_F32_SUM = 0, 1, 2
 OPT_ONESHOT_MAX_BYTES, OPT_TIMEOUT_MS, OPT_MAX_BLOCKS, OPT_PIPE_GROUP = 1, 2, 3, 4
 OPT_HOST_CHUNK_BYTES = 5
 OPT_TRACE = 6
+OPT_VIEW_CHUNK_TILES = 7
+VIEW_MULTICAST = 1
+VIEW_HANDLE_BYTES = 128
 IPC_HANDLE_BYTES = 64
 MAX_WORLD = 8
 TILE_BYTES = 2048
@@ -29,6 +33,19 @@ SIGNATURES = {
                               _c.c_void_p, _c.c_int]),
     "ga_allreduce_tensors": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
                                         _c.c_int, _c.c_void_p, _c.c_int]),
+    "ga_allreduce_tensors_ex": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
+                                           _c.c_int, _c.c_void_p, _c.c_int, _c.c_int]),
+    "ga_broadcast_tensors": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
+                                        _c.c_int, _c.c_void_p]),
+    "ga_view_create": (_c.c_int, [_c.c_void_p, _c.c_size_t, _c.c_int]),
+    "ga_view_export": (_c.c_int, [_c.c_void_p, _c.c_char_p]),
+    "ga_view_open": (_c.c_int, [_c.c_void_p, _c.c_char_p]),
+    "ga_view_bind": (_c.c_int, [_c.c_void_p]),
+    "ga_view_ptr": (_c.c_void_p, [_c.c_void_p, _c.c_int]),
+    "ga_view_bytes": (_c.c_size_t, [_c.c_void_p]),
+    "ga_view_has_multicast": (_c.c_int, [_c.c_void_p]),
+    "ga_multicast_supported": (_c.c_int, [_c.c_int]),
+    "ga_average_view": (_c.c_int, [_c.c_void_p, _c.c_size_t, _c.c_int, _c.c_void_p, _c.c_int]),
     "ga_allreduce_bucket": (_c.c_int, [_c.c_void_p, _c.c_size_t, _c.c_int, _c.c_void_p, _c.c_int]),
     "ga_average_host": (_c.c_int, [_c.c_void_p, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
                                    _c.c_void_p, _c.c_int]),
@@ -51,6 +68,7 @@ SIGNATURES = {
     "ga_synchronize": (_c.c_int, [_c.c_void_p, _c.c_void_p]),
     "ga_average_static": (_c.c_int, [_c.c_int, _c.c_int, _c.POINTER(_c.c_void_p), _c.POINTER(_c.c_int64), _c.c_int,
                                      _c.c_void_p, _c.c_int]),
+    "ga_static_status": (_c.c_int, [_c.c_int, _c.c_void_p]),
     "ga_close_peers": (_c.c_int, [_c.c_void_p]),
     "ga_destroy": (_c.c_int, [_c.c_void_p]),
 }

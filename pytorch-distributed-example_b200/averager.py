@@ -12,6 +12,8 @@ from ._lib import GradAvgError, check, load_library
 AUTO, ONESHOT, TWOSHOT = _lib.VARIANT_AUTO, _lib.VARIANT_ONESHOT, _lib.VARIANT_TWOSHOT
 ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE = _lib.VARIANT_ONESHOT_PUSH, _lib.VARIANT_TWOSHOT_PUSH, _lib.VARIANT_TWOSHOT_PIPE
 HOSTED_DIRECT = _lib.VARIANT_HOSTED_DIRECT
+VIEW, NVLS = _lib.VARIANT_VIEW, _lib.VARIANT_NVLS
+_VIEW_VARIANTS = {"auto": AUTO, None: AUTO, AUTO: AUTO, "view": VIEW, VIEW: VIEW, "nvls": NVLS, NVLS: NVLS}
 _VARIANTS = {"auto": AUTO, "oneshot": ONESHOT, "1shot": ONESHOT, "twoshot": TWOSHOT, "2shot": TWOSHOT,
              "oneshot_push": ONESHOT_PUSH, "twoshot_push": TWOSHOT_PUSH, "twoshot_pipe": TWOSHOT_PIPE, TWOSHOT_PIPE: TWOSHOT_PIPE,
              "hosted_direct": _lib.VARIANT_HOSTED_DIRECT, _lib.VARIANT_HOSTED_DIRECT: _lib.VARIANT_HOSTED_DIRECT,
@@ -78,6 +80,7 @@ class GradAverager:
         self._launch_base = 0
         self._ptr_cache = {}
         self._plans = {}
+        self._adopted = None                   # (param ids, gradient addresses, bytes) once adopt() has run
         if capacity_bytes:
             self._create(capacity_bytes)
 
@@ -131,6 +134,10 @@ class GradAverager:
         if self._ctx is not None and need_bytes <= self._capacity:
             return
         if self._ctx is not None:
+            if self._adopted is not None or int(self._lib.ga_view_bytes(self._ctx)):
+                raise GradAvgError(_lib.GA_ECAPACITY, "this call needs a %d-byte bucket but the context (%d bytes) holds a "
+                                   "gradient view region and cannot be re-created: size the averager with capacity_bytes "
+                                   "up front" % (need_bytes, self._capacity))
             # Every rank sees the same sizes, so every rank takes this branch in the same call.
             self.close()
         self._create(max(need_bytes, 32 << 20))     # room for two one-shot staging halves of small sets
@@ -149,6 +156,7 @@ class GradAverager:
             self._lib.ga_destroy(self._ctx)
             self._ctx = None
             self._ptr_cache.clear()
+            self._adopted = None
 
     def __del__(self):
         try:
@@ -209,11 +217,16 @@ class GradAverager:
             v = self._variant if variant is None else _VARIANTS[variant]
             check(self._lib.ga_allreduce_tensors(self._ctx, ptrs, numel, n, op, ctypes.c_void_p(stream), v))
 
-    def _run_params(self, per_rank_params, variant):
+    def _run_params(self, per_rank_params, variant, max_blocks=0):
         """Hot path of the training loop.  The element counts of a parameter list never change, so
         they are laid out once per list (keyed by the identity of its parameters); every call then
         only re-reads the gradient pointers and checks dtype / device / contiguity."""
         flat = [p for ps in per_rank_params for p in ps]
+        if self._adopted is not None and self._try_view(flat, variant):
+            return
+        if variant in (VIEW, NVLS, "view", "nvls"):
+            raise GradAvgError(_lib.GA_ESTATE, "variant %r needs adopted gradients that are still in their views "
+                               "(adopt(); zero_grad(set_to_none=False))" % (variant,))
         key = tuple(map(id, flat))
         plan = self._plans.get(key)
         if plan is None:
@@ -255,7 +268,11 @@ class GradAverager:
                 k += 1
             stream = torch.cuda.current_stream(self.device).cuda_stream
             v = self._variant if variant is None else _VARIANTS[variant]
-            check(self._lib.ga_average(self._ctx, ptrs, numel, n, ctypes.c_void_p(stream), v))
+            if max_blocks:
+                check(self._lib.ga_allreduce_tensors_ex(self._ctx, ptrs, numel, n, _lib.OP_F32_AVG, ctypes.c_void_p(stream), v,
+                                                        int(max_blocks)))
+            else:
+                check(self._lib.ga_average(self._ctx, ptrs, numel, n, ctypes.c_void_p(stream), v))
 
     def average_gradients(self, params, variant=None):
         """`Trainer.average_gradients` (mnist/main.py:122-127) for one rank: every `p.grad` is
@@ -316,6 +333,161 @@ class GradAverager:
             stream = torch.cuda.current_stream(self.device).cuda_stream
             v = self._variant if variant is None else _VARIANTS[variant]
             check(self._lib.ga_average_host(self._ctx, ptrs, numel, n, ctypes.c_void_p(stream), v))
+
+    # -- gradients as views of the peer-mapped region ---------------------------
+    def _create_view(self, nbytes, multicast):
+        """Collective: allocates the view region and maps every peer's (mnist/main.py:199-203's group
+        carries the handles, like the bucket's)."""
+        flags = _lib.VIEW_MULTICAST if multicast else 0
+        check(self._lib.ga_view_create(self._ctx, int(nbytes), flags))
+        if self._local or self.world_size == 1:
+            if not self._local:
+                mine = ctypes.create_string_buffer(_lib.VIEW_HANDLE_BYTES)
+                check(self._lib.ga_view_export(self._ctx, mine))
+                check(self._lib.ga_view_open(self._ctx, mine.raw))
+            return
+        import torch.distributed as dist
+        mine = ctypes.create_string_buffer(_lib.VIEW_HANDLE_BYTES)
+        check(self._lib.ga_view_export(self._ctx, mine))
+        backend = dist.get_backend(self._group)
+        dev = self.device if "nccl" in str(backend) else torch.device("cpu")
+        t = torch.frombuffer(bytearray(mine.raw), dtype=torch.uint8).to(dev)
+        out = [torch.empty_like(t) for _ in range(self.world_size)]
+        dist.all_gather(out, t, group=self._group)
+        blob = b"".join(bytes(o.cpu().numpy().tobytes()) for o in out)
+        check(self._lib.ga_view_open(self._ctx, blob))
+        dist.barrier(group=self._group)      # every rank has fetched the descriptors and joined the multicast object
+        check(self._lib.ga_view_bind(self._ctx))
+        dist.barrier(group=self._group)      # every rank's memory is bound before anybody issues multimem.*
+
+    def create_view(self, nbytes, multicast=True):
+        """Flat form: a `nbytes` region per hosted rank for `view_tensor` / `allreduce_view`."""
+        with self._lock:
+            self._ensure(int(nbytes))
+            if not int(self._lib.ga_view_bytes(self._ctx)):
+                self._create_view(int(nbytes), multicast)
+            elif int(self._lib.ga_view_bytes(self._ctx)) < int(nbytes):
+                raise GradAvgError(_lib.GA_ECAPACITY, "the view region is smaller than %d bytes" % nbytes)
+
+    @property
+    def has_multicast(self):
+        return bool(self._ctx is not None and self._lib.ga_view_has_multicast(self._ctx))
+
+    def view_tensor(self, nbytes=None, local_rank=0, dtype=torch.float32, offset=0, shape=None):
+        """Tensor aliasing hosted rank `local_rank`'s view region."""
+        base = self._lib.ga_view_ptr(self._ctx, local_rank)
+        if not base:
+            raise GradAvgError(_lib.GA_ESTATE, "no view region (create_view / adopt)")
+        nbytes = int(self._lib.ga_view_bytes(self._ctx)) - offset if nbytes is None else nbytes
+        t = self._view(int(base) + int(offset), int(nbytes), dtype)
+        return t if shape is None else t.view(shape)
+
+    def allreduce_view(self, nbytes, op=_lib.OP_F32_AVG, variant=None):
+        """`ga_average_view`: in place on the first nbytes of every rank's view region."""
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with self._lock:
+            check(self._lib.ga_average_view(self._ctx, int(nbytes), op, ctypes.c_void_p(stream), _VIEW_VARIANTS[variant]))
+
+    def adopt(self, modules, multicast=True, optimizer=None):
+        """Makes every `p.grad` a view into the peer-mapped region, so that `average_gradients` works
+        in place: no pack, no unpack (the steps either side only touch p.grad: mnist/main.py:91-92,96).
+
+        modules: the replica (or its parameters) of this rank, or one per hosted rank.  Existing
+        gradients are copied into their views.  The views survive only while nothing replaces
+        `p.grad`: use `optimizer.zero_grad(set_to_none=False)` -- pass `optimizer=` and its
+        `zero_grad` gets that default.  If a gradient is found outside its view at averaging time
+        (`zero_grad()` dropped it and autograd re-allocated it), that call silently takes the drop-in
+        pack/unpack path instead, so correctness never depends on the views.  Collective."""
+        if isinstance(modules, torch.nn.Module) or not isinstance(modules, (list, tuple)):
+            modules = [modules]
+        if len(modules) != self.n_local and self.n_local == 1:
+            modules = [modules]                   # a plain list of parameters
+        per_rank = [list(m.parameters()) if isinstance(m, torch.nn.Module) else list(m) for m in modules]
+        if len(per_rank) != self.n_local:
+            raise GradAvgError(_lib.GA_EINVAL, "need %d parameter lists" % self.n_local)
+        numels = [p.numel() for p in per_rank[0]]
+        if any([p.numel() for p in ps] != numels for ps in per_rank[1:]):
+            raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different parameter sizes")
+        need = bucket_bytes(numels)
+        with self._lock:
+            if self._adopted is not None:
+                raise GradAvgError(_lib.GA_ESTATE, "this averager has already adopted a parameter list")
+            self._ensure(max(need, 32 << 20))
+            self._create_view(need, multicast)
+            addrs = []
+            for l, ps in enumerate(per_rank):
+                off = 0
+                for p, n in zip(ps, numels):
+                    if p.dtype != torch.float32 or not p.is_cuda or p.device != self.device:
+                        raise GradAvgError(_lib.GA_EINVAL, "adopt needs float32 parameters on %s" % (self.device,))
+                    g = self.view_tensor(n * 4, l, torch.float32, off, tuple(p.shape))
+                    if p.grad is not None:
+                        g.copy_(p.grad)
+                    else:
+                        g.zero_()
+                    p.grad = g
+                    addrs.append(g.data_ptr())
+                    off += _tiles(n) * _lib.TILE_BYTES
+            torch.cuda.current_stream(self.device).synchronize()
+            flat = [p for ps in per_rank for p in ps]
+            self._adopted = (tuple(map(id, flat)), addrs, need, flat)
+        if optimizer is not None:
+            import functools
+            optimizer.zero_grad = functools.partial(optimizer.zero_grad, set_to_none=False)
+        return self
+
+    def _try_view(self, flat, variant):
+        """In-place averaging if `flat` is the adopted list and every gradient still sits in its view."""
+        ad = self._adopted
+        if ad is None or variant not in _VIEW_VARIANTS:
+            return False
+        ids, addrs, need, _keep = ad
+        if len(flat) != len(ids):
+            return False
+        for p, i, a in zip(flat, ids, addrs):
+            g = p.grad
+            if id(p) != i or g is None or g.data_ptr() != a:
+                return False
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        with self._lock:
+            check(self._lib.ga_average_view(self._ctx, need, _lib.OP_F32_AVG, ctypes.c_void_p(stream), _VIEW_VARIANTS[variant]))
+        return True
+
+    # -- parameter broadcast (SURVEY.md 8f-3) -----------------------------------------------------
+    def broadcast_(self, tensors, root=0):
+        """Replicates rank `root`'s tensors into every other rank's (in place).  The reference never
+        makes its replicas start equal (no seed, no broadcast: mnist/main.py:185).  One list per
+        hosted rank; any dense 4-byte-multiple dtype (moved as 32-bit words)."""
+        if torch.is_tensor(tensors):
+            tensors = [[tensors]]
+        elif tensors and torch.is_tensor(tensors[0]):
+            tensors = [list(tensors)]
+        if len(tensors) != self.n_local:
+            raise GradAvgError(_lib.GA_EINVAL, "got %d tensor lists for %d hosted rank(s)" % (len(tensors), self.n_local))
+        words = []
+        for ts in tensors:
+            row = []
+            for t in ts:
+                if not t.is_cuda or t.device != self.device or not _dense(t) or (t.numel() * t.element_size()) % 4:
+                    raise GradAvgError(_lib.GA_EINVAL, "broadcast needs dense CUDA tensors of a 4-byte-multiple size on %s" % (self.device,))
+                row.append((t.data_ptr(), t.numel() * t.element_size() // 4))
+            words.append(row)
+        n = len(words[0])
+        if any([w[1] for w in row] != [w[1] for w in words[0]] for row in words[1:]):
+            raise GradAvgError(_lib.GA_EINVAL, "hosted ranks passed different tensor sizes")
+        with self._lock:
+            self._ensure(bucket_bytes([w[1] for w in words[0]]))
+            ptrs = (ctypes.c_void_p * (n * len(words)))(*[w[0] for row in words for w in row])
+            numel = (ctypes.c_int64 * n)(*[w[1] for w in words[0]])
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            check(self._lib.ga_broadcast_tensors(self._ctx, ptrs, numel, n, int(root), ctypes.c_void_p(stream)))
+
+    def broadcast_parameters(self, modules, root=0):
+        """Parameters and buffers of the replica(s) become rank `root`'s."""
+        if isinstance(modules, torch.nn.Module):
+            modules = [modules]
+        lists = [[t.data for t in list(m.parameters()) + list(m.buffers()) if t.numel()] for m in modules]
+        self.broadcast_(lists, root=root)
 
     # -- bucket-direct form (size sweep, NCCL comparison) -------------------------------------
     def reserve(self, nbytes):

@@ -23,170 +23,9 @@
 // kept in device memory so that a launch can be replayed from a CUDA graph.  Nothing here is a
 // contraction, so no tensor cores; the kernels are HBM-bound on one GPU and NVLink-bound across
 // GPUs.  Build: see __graft_entry__.build().
-#include <cuda_runtime.h>
-#include <stdarg.h>
-#include <stdint.h>
-#include <stdio.h>
-#include <stdlib.h>
-#include <string.h>
-
-#include "../../include/gradavg.h"
+#include "gradavg_internal.cuh"
 
 namespace {
-
-// ------------------------------------------------------------------------------------------
-// constants and device-visible structures
-// ------------------------------------------------------------------------------------------
-constexpr int kMaxWorld = GA_MAX_WORLD;
-constexpr int kTileVecs = 128;                 // 16-byte vectors per warp tile
-constexpr int kTileBytes = kTileVecs * 16;     // 2 KiB
-constexpr int kTileElems = kTileVecs * 4;      // 512 32-bit elements
-constexpr int kLaneVecs = kTileVecs / 32;      // 4 vectors per lane per tile
-constexpr int kThreads = 512;                  // 16 warps per block
-constexpr int kMaxBlocks = 1024;               // flag rows per rank
-constexpr int kInlineSegs = 128;               // pointer-table entries carried in kernel params
-constexpr int kSegRing = 4;                    // staging slots for larger pointer tables
-constexpr int kTraceSlots = 16;                // phase timestamps per block when tracing is on
-constexpr int kHostChunks = 64;                // most chunks one ga_average_host call is cut into
-
-typedef uint4 Vec;
-
-struct Seg {               // one gradient tensor of one rank
-    const void *ptr;       // device pointer (re-read every call)
-    uint32_t start_tile;   // first bucket tile of this tensor
-    uint32_t numel;        // 32-bit elements
-};
-
-struct Pad {                                    // head of every rank's IPC allocation
-    uint32_t ready[kMaxBlocks][kMaxWorld];      // [block][src rank]: src packed its tiles (epoch)
-    uint32_t mid[kMaxBlocks][kMaxWorld];        // [block][src rank]: src reduced its shard (epoch)
-    uint32_t done[kMaxWorld];                   // [src rank]: src finished reading my bucket (epoch)
-    uint32_t finished_blocks;                   // local block counter of the running launch
-    uint32_t epoch;                             // last flag value this rank used; read at kernel start, advanced
-                                                // by the last block, so a launch carries no host-side counter
-                                                // and can be replayed from a CUDA graph
-    uint32_t last_kind;                         // 1 if this rank's previous launch was a double-buffered one-shot
-                                                // push (its successor of the same kind need not wait for `done`)
-    uint32_t reserved[21];
-};
-constexpr size_t kPadBytes = (sizeof(Pad) + 4095) / 4096 * 4096;
-
-struct Params {
-    void *send[kMaxWorld];      // every rank's bucket, by global rank (peer-mapped)
-    Pad *pad[kMaxWorld];        // every rank's flag pad, by global rank (peer-mapped)
-    void *recv[kMaxWorld];      // result regions of the hosted ranks, by local index
-    void *gather[kMaxWorld];    // every rank's gather region, by global rank (push variants write into it)
-    const Seg *dev_segs;        // [n_local][n_seg], or nullptr -> inline_segs
-    int *status;                // host-mapped error word
-    unsigned long long timeout_ns;
-    uint32_t n_seg;
-    uint32_t total_tiles;
-    uint32_t shard_tiles;       // two-shot: tiles per rank shard
-    int rank_base;
-    int direct;                 // 1: bucket-direct (no pack, result -> recv)
-    unsigned long long parity_stride;   // one-shot push: byte offset of the odd-epoch staging half (0 = single buffer)
-    unsigned long long *trace;  // optional phase timestamps, kTraceSlots per block (GA_OPT_TRACE)
-    uint32_t rounds;            // pipelined two-shot push: rounds per launch (flags use epoch .. epoch+rounds-1)
-    uint32_t group;             //   and tile slots per block per round
-    Seg inline_segs[kInlineSegs];
-};
-
-// ------------------------------------------------------------------------------------------
-// element operations
-// ------------------------------------------------------------------------------------------
-template <int OP> struct ElemOp;
-template <> struct ElemOp<GA_OP_F32_AVG> {
-    // __fadd_rn / __fdiv_rn: single IEEE binary32 operations, never contracted or replaced by
-    // a reciprocal multiply (x/3.0f != x*(1/3.0f)).
-    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) {
-        return __float_as_uint(__fadd_rn(__uint_as_float(a), __uint_as_float(b)));
-    }
-    static __device__ __forceinline__ uint32_t fin(uint32_t a, float w) {
-        return __float_as_uint(__fdiv_rn(__uint_as_float(a), w));
-    }
-};
-template <> struct ElemOp<GA_OP_F32_SUM> {
-    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) {
-        return __float_as_uint(__fadd_rn(__uint_as_float(a), __uint_as_float(b)));
-    }
-    static __device__ __forceinline__ uint32_t fin(uint32_t a, float) { return a; }
-};
-template <> struct ElemOp<GA_OP_I32_SUM> {
-    static __device__ __forceinline__ uint32_t add(uint32_t a, uint32_t b) { return a + b; }
-    static __device__ __forceinline__ uint32_t fin(uint32_t a, float) { return a; }
-};
-
-// ------------------------------------------------------------------------------------------
-// flags
-// ------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p) {
-    uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ unsigned long long global_ns() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-
-// Phase timestamp of this block (thread 0), only when the context has tracing switched on.
-#define GA_TRACE(p, k)                                                                                   \
-    do {                                                                                                 \
-        if ((p).trace && threadIdx.x == 0)                                                               \
-            (p).trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kTraceSlots + (k)] = global_ns(); \
-    } while (0)
-
-// Spin until *flag has reached `target` (wrap-safe).  Returns false on timeout.
-__device__ __forceinline__ bool spin_until(const uint32_t *flag, uint32_t target, unsigned long long timeout_ns) {
-    unsigned long long t0 = 0;
-    uint32_t spins = 0;
-    while ((int32_t)(ld_relaxed_sys(flag) - target) < 0) {
-        if ((++spins & 1023u) == 0 && timeout_ns) {
-            unsigned long long now = global_ns();
-            if (t0 == 0) t0 = now;
-            else if (now - t0 > timeout_ns) return false;
-        }
-    }
-    return true;
-}
-
-// Block-wide wait for one flag per source rank.  ONE thread polls the W words in turn (they turn
-// up within a round trip of each other) and issues ONE system-scope fence: with eight polling
-// threads each needed its own fence, and system fences are what these barriers cost (more blocks
-// made every variant slower until this was changed).  Returns false for the whole block on timeout.
-template <int W>
-__device__ __forceinline__ bool wait_flags(const uint32_t *row, uint32_t target, const Params &p, int *s_abort) {
-    if (threadIdx.x == 0) {
-#pragma unroll 1
-        for (int s = 0; s < W; ++s) {
-            if (!spin_until(row + s, target, p.timeout_ns)) {
-                *s_abort = 1;
-                *(volatile int *)p.status = GA_ETIMEOUT;
-                break;
-            }
-        }
-        asm volatile("fence.acq_rel.sys;" ::: "memory");   // acquire: peers' data before the block's loads of it
-    }
-    __syncthreads();
-    return *s_abort == 0;
-}
-
-__device__ __forceinline__ void st_relaxed_sys(uint32_t *p, uint32_t v) {
-    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Block-wide: everything this block wrote so far becomes visible (one system-scope fence by one
-// thread, after the block barrier), then that thread posts the flag word into every rank's pad.
-template <int W>
-__device__ __forceinline__ void raise_flags(const Params &p, size_t word_off, uint32_t value) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        asm volatile("fence.acq_rel.sys;" ::: "memory");
-#pragma unroll
-        for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + word_off, value);
-    }
-}
 
 // ------------------------------------------------------------------------------------------
 // tile movers (one warp moves one 2 KiB tile; lane l owns vectors l, l+32, l+64, l+96)
@@ -895,6 +734,83 @@ __global__ void __launch_bounds__(kThreads, 2) ga_hosted_direct_kernel(const __g
     }
 }
 
+// Parameter broadcast: the reference builds Net() on every rank and relies on
+// identical seeds it never sets (/root/reference/mnist/main.py:185).  The root packs its tensors
+// straight into every peer's gather region (remote stores, pack folded in), flags per block column;
+// the peers unpack their column into their own tensors.  Same flag protocol and epoch as the averaging
+// kernels, so calls can be mixed freely on one context.
+template <int W>
+__global__ void __launch_bounds__(kThreads, 2) ga_bcast_kernel(const __grid_constant__ Params p) {
+    __shared__ int s_abort;
+    __shared__ int s_last;
+    const int ly = blockIdx.y;
+    const int r = p.rank_base + ly;
+    const int b = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int wpb = blockDim.x >> 5;
+    const uint32_t stride = gridDim.x * wpb;
+    const uint32_t first = b * wpb + warp;
+    const uint32_t T = p.total_tiles;
+    const int root = p.root;
+
+    Pad *mypad = p.pad[r];
+    const uint32_t epoch = ld_relaxed_sys(&mypad->epoch) + 1;
+    const Seg *segs = (p.dev_segs ? p.dev_segs : p.inline_segs) + (size_t)ly * p.n_seg;
+    const int n_seg = (int)p.n_seg;
+    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
+    __syncthreads();
+    // every rank has left its previous launch: the gather regions are free to be overwritten
+    if (!wait_flags<W>(mypad->done, epoch - 1, p, &s_abort)) return;
+
+    if (r == root) {
+        for (uint32_t t = first; t < T; t += stride) {
+            const Seg sg = segs[find_seg(segs, n_seg, t)];
+            Vec v[kLaneVecs];
+            load_grad_tile(sg, t, lane, v);
+#pragma unroll 1
+            for (int jj = 1; jj < W; ++jj) {
+                Vec *dst = (Vec *)p.gather[(r + jj) % W] + (size_t)t * kTileVecs + lane;
+#pragma unroll
+                for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+            }
+        }
+        raise_flags<W>(p, offsetof(Pad, ready) / 4 + (size_t)b * kMaxWorld + root, epoch);
+    } else {
+        if (threadIdx.x == 0) {
+            if (!spin_until(&mypad->ready[b][root], epoch, p.timeout_ns)) {
+                s_abort = 1;
+                *(volatile int *)p.status = GA_ETIMEOUT;
+            }
+            asm volatile("fence.acq_rel.sys;" ::: "memory");
+        }
+        __syncthreads();
+        if (s_abort) return;
+        const Vec *mygather = (const Vec *)p.gather[r];
+        for (uint32_t t = first; t < T; t += stride) {
+            const Seg sg = segs[find_seg(segs, n_seg, t)];
+            const Vec *src = mygather + (size_t)t * kTileVecs + lane;
+            Vec v[kLaneVecs];
+#pragma unroll
+            for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcg(src + u * 32);
+            store_grad_vecs<kLaneVecs>(sg, t, lane, 0, v);
+        }
+    }
+
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x == 0) {
+        mypad->finished_blocks = 0; mypad->epoch = epoch; mypad->last_kind = 0;
+        asm volatile("fence.acq_rel.sys;" ::: "memory");
+#pragma unroll
+        for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + offsetof(Pad, done) / 4 + r, epoch);
+    }
+}
+
 // Launched only when a bucket-direct call follows a tensor-list call: the caller is about to
 // overwrite the bucket from the host side of the stream, so every peer must have finished
 // reading it (tensor-list calls check this lazily, at the start of the NEXT kernel).
@@ -907,12 +823,14 @@ __global__ void ga_drain_kernel(const Pad *const *pads, int n_local, int world,
     }
 }
 
+}  // namespace
+
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-thread_local char g_err[512] = "";
+static thread_local char g_err[512] = "";
 
-int fail(int code, const char *fmt, ...) {
+int ga_fail(int code, const char *fmt, ...) {
     va_list ap;
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
@@ -920,30 +838,29 @@ int fail(int code, const char *fmt, ...) {
     return code;
 }
 
-#define CUDA_TRY(expr)                                                                         \
-    do {                                                                                       \
-        cudaError_t e_ = (expr);                                                               \
-        if (e_ != cudaSuccess)                                                                 \
-            return fail(GA_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
-    } while (0)
-
-// Makes `device` current for the duration of an entry point and puts the caller's device back on
-// the way out, so that a process driving several GPUs is not left on another device by a call.
-struct DeviceGuard {
-    int prev = -1;
-    cudaError_t err;
-    explicit DeviceGuard(int device) {
-        err = cudaGetDevice(&prev);
-        if (err == cudaSuccess && prev != device) err = cudaSetDevice(device);
-        else if (err != cudaSuccess) { prev = -1; err = cudaSetDevice(device); }
-        if (prev == device) prev = -1;          // nothing to restore
+// Launches of one context share its flag epoch and staging regions, so they must be ordered with
+// respect to each other.  On one stream they are; when the caller comes back on ANOTHER stream the
+// new stream is made to wait for the previous launch here.  (While either stream is being captured
+// nothing is inserted: inside a graph the caller's own edges are the ordering.)
+int ga_order_stream(ga_ctx *c, void *stream) {
+    if (c->have_last_stream && c->last_stream != stream) {
+        cudaStreamCaptureStatus a = cudaStreamCaptureStatusNone, b = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing((cudaStream_t)c->last_stream, &a) != cudaSuccess) { cudaGetLastError(); a = cudaStreamCaptureStatusInvalidated; }
+        if (cudaStreamIsCapturing((cudaStream_t)stream, &b) != cudaSuccess) { cudaGetLastError(); b = cudaStreamCaptureStatusInvalidated; }
+        if (a == cudaStreamCaptureStatusNone && b == cudaStreamCaptureStatusNone) {
+            if (!c->order_event) CUDA_TRY(cudaEventCreateWithFlags(&c->order_event, cudaEventDisableTiming));
+            if (cudaEventRecord(c->order_event, (cudaStream_t)c->last_stream) == cudaSuccess)
+                CUDA_TRY(cudaStreamWaitEvent((cudaStream_t)stream, c->order_event, 0));
+            else
+                cudaGetLastError();      // the previous stream no longer exists: nothing left to order against
+        }
     }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-};
-#define ENTER_DEVICE(dev)                                                                      \
-    DeviceGuard device_guard_(dev);                                                            \
-    if (device_guard_.err != cudaSuccess)                                                      \
-        return fail(GA_ECUDA, "cudaSetDevice(%d) failed: %s", (dev), cudaGetErrorString(device_guard_.err))
+    c->last_stream = stream;
+    c->have_last_stream = true;
+    return GA_OK;
+}
+
+namespace {
 
 typedef void (*KernelFn)(Params);
 
@@ -982,7 +899,22 @@ template <int W> KernelFn pick_variant(int variant, int op) {
     }
     return pick_op<W, GA_VARIANT_ONESHOT>(op);
 }
+constexpr int kVariantBcast = 15;    // internal: ga_bcast_kernel through the common launch path
+KernelFn pick_bcast(int world) {
+    switch (world) {
+        case 1: return (KernelFn)ga_bcast_kernel<1>;
+        case 2: return (KernelFn)ga_bcast_kernel<2>;
+        case 3: return (KernelFn)ga_bcast_kernel<3>;
+        case 4: return (KernelFn)ga_bcast_kernel<4>;
+        case 5: return (KernelFn)ga_bcast_kernel<5>;
+        case 6: return (KernelFn)ga_bcast_kernel<6>;
+        case 7: return (KernelFn)ga_bcast_kernel<7>;
+        case 8: return (KernelFn)ga_bcast_kernel<8>;
+    }
+    return nullptr;
+}
 KernelFn pick_kernel(int world, int variant, int op) {
+    if (variant == kVariantBcast) return pick_bcast(world);
     switch (world) {
         case 1: return pick_variant<1>(variant, op);
         case 2: return pick_variant<2>(variant, op);
@@ -997,41 +929,6 @@ KernelFn pick_kernel(int world, int variant, int op) {
 }
 
 }  // namespace
-
-struct ga_ctx {
-    int world, rank_base, n_local, device;
-    size_t capacity_bytes;          // per rank, multiple of kTileBytes
-    size_t region_bytes;            // capacity + slack: two-shot push stages world * ceil(T / world) >= T tiles
-    void *base[kMaxWorld];          // own allocations [Pad | bucket], by local index
-    void *recv[kMaxWorld];          // own result regions, by local index
-    void *peer_base[kMaxWorld];     // IPC-opened peer allocations, by global rank (nullptr = not opened)
-    void *send_all[kMaxWorld];      // by global rank
-    void *gather_all[kMaxWorld];    // by global rank (second half of the IPC allocation)
-    Pad *pad_all[kMaxWorld];        // by global rank
-    bool opened, broken;
-    int sm_count, blocks_per_sm[8];                  // by variant; 0 = not queried yet
-    int max_blocks_opt;
-    unsigned long long *trace_dev;  // GA_OPT_TRACE: kMaxBlocks * n_local * kTraceSlots words, or nullptr
-    int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
-    size_t oneshot_max_bytes;
-    size_t pipe_min_bytes;          // pipelined kernel: one round below min, 32 MiB rounds from min on; AUTO stops
-    size_t pipe_max_bytes;          //   using it above max (N=4/8 sweeps: 3-10 % gain up to 128 MiB, a loss beyond)
-    unsigned long long timeout_ns;
-    int *status_host, *status_dev;
-    Seg *seg_host[kSegRing], *seg_dev[kSegRing];
-    size_t seg_cap;                 // entries per ring slot
-    cudaEvent_t seg_event[kSegRing];
-    bool seg_used[kSegRing];
-    int seg_pos;
-    uint64_t launches;
-    int last_blocks, last_threads;
-    bool last_was_tensor_call;      // previous launch checks its readers lazily (see ga_drain_kernel)
-    const Pad **own_pads_dev;       // device array of the hosted ranks' pads, for ga_drain_kernel
-    // ga_average_host pipeline: copy-in / kernel / copy-out streams and per-chunk events
-    cudaStream_t s_in, s_k, s_out;
-    cudaEvent_t ev_start, ev_done, ev_in[kHostChunks], ev_k[kHostChunks];
-    size_t host_chunk_bytes;
-};
 
 namespace {
 
@@ -1048,6 +945,8 @@ void set_auto_thresholds(ga_ctx *c) {
     c->pipe_min_bytes = (size_t)32 << 20;
     c->pipe_max_bytes = (size_t)128 << 20;
 }
+
+int create_body(ga_ctx *c, int device);
 
 int create_common(int rank_base, int n_local, int world, int device, size_t capacity_bytes, ga_ctx **out) {
     if (!out) return fail(GA_EINVAL, "out is NULL");
@@ -1072,7 +971,23 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->host_chunk_bytes = (size_t)8 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
     if (env) c->timeout_ns = strtoull(env, nullptr, 10) * 1000000ull;
+    const int rc = create_body(c, device);
+    if (rc != GA_OK) {
+        // whatever was allocated before the failing call is released (ga_destroy tolerates the gaps);
+        // the message of the failure is kept
+        char keep[sizeof(g_err)];
+        memcpy(keep, g_err, sizeof keep);
+        ga_destroy(c);
+        memcpy(g_err, keep, sizeof keep);
+        return rc;
+    }
+    c->opened = (n_local == world);
+    *out = c;
+    return GA_OK;
+}
 
+int create_body(ga_ctx *c, int device) {
+    const int n_local = c->n_local, rank_base = c->rank_base;
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
@@ -1095,8 +1010,6 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
         CUDA_TRY(cudaMemcpy(c->own_pads_dev, own, sizeof(own), cudaMemcpyHostToDevice));
     }
     CUDA_TRY(cudaDeviceSynchronize());
-    c->opened = (n_local == world);
-    *out = c;
     return GA_OK;
 }
 
@@ -1130,7 +1043,7 @@ int blocks_per_sm(ga_ctx *c, KernelFn fn, int variant) {
 
 // Common launch path.  `segs` (n_local * n_seg entries, rank-major) is nullptr for bucket-direct.
 int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int op, void *stream, int variant, bool direct,
-           size_t byte_offset = 0) {
+           size_t byte_offset = 0, int root = 0, int max_blocks = 0) {
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
     if (*(volatile int *)c->status_host != 0) {
         // a kernel of this context already gave up on a peer: fail now instead of queueing more
@@ -1145,7 +1058,8 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
         if (direct && variant == GA_VARIANT_HOSTED_DIRECT)
             variant = (size_t)total_tiles * kTileBytes <= c->oneshot_max_bytes ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
     }
-    if (variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_HOSTED_DIRECT) return fail(GA_EINVAL, "unknown variant %d", variant);
+    if ((variant < GA_VARIANT_ONESHOT || variant > GA_VARIANT_HOSTED_DIRECT) && variant != kVariantBcast)
+        return fail(GA_EINVAL, "unknown variant %d (GA_VARIANT_VIEW / GA_VARIANT_NVLS belong to ga_average_view)", variant);
     if (variant == GA_VARIANT_HOSTED_DIRECT && c->n_local != c->world)
         return fail(GA_EINVAL, "GA_VARIANT_HOSTED_DIRECT needs every rank hosted in this process (ga_create_local)");
     if (variant == GA_VARIANT_HOSTED_DIRECT && direct)
@@ -1177,6 +1091,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     p.rank_base = c->rank_base;
     p.direct = direct ? 1 : 0;
     p.trace = c->trace_dev;
+    p.root = root;
 
     if (segs) {
         const size_t entries = (size_t)n_seg * c->n_local;
@@ -1204,6 +1119,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
     int resident = blocks_per_sm(c, fn, variant) * c->sm_count / c->n_local;
     if (resident > kMaxBlocks) resident = kMaxBlocks;
     if (c->max_blocks_opt > 0 && resident > c->max_blocks_opt) resident = c->max_blocks_opt;
+    if (max_blocks > 0 && resident > max_blocks) resident = max_blocks;       // per-call cap (overlap mode)
     if (resident < 1) resident = 1;
     int blocks = (int)((slots + wpb - 1) / wpb);
     uint32_t rounds = 1;
@@ -1222,7 +1138,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
                 if (group > 16) group = 16;
             }
         } else {
-            if (c->max_blocks_opt == 0 && resident > c->sm_count / c->n_local) resident = c->sm_count / c->n_local;
+            if (c->max_blocks_opt == 0 && max_blocks == 0 && resident > c->sm_count / c->n_local) resident = c->sm_count / c->n_local;
             if (resident < 1) resident = 1;
             if (group == 0) {
                 const size_t per_slot = (size_t)c->world * kTileBytes * (size_t)resident;
@@ -1262,6 +1178,7 @@ int launch(ga_ctx *c, const Seg *segs, uint32_t n_seg, uint32_t total_tiles, int
         // one launch over the tiles, every rank's tensors addressed directly: no flags, no epoch
         int all = blocks_per_sm(c, fn, variant) * c->sm_count;
         if (c->max_blocks_opt > 0 && all > c->max_blocks_opt) all = c->max_blocks_opt;
+        if (max_blocks > 0 && all > max_blocks) all = max_blocks;
         blocks = (int)((total_tiles + wpb - 1) / wpb);
         if (blocks > all) blocks = all;
         if (blocks < 1) blocks = 1;
@@ -1389,7 +1306,16 @@ int ga_open_peers(ga_ctx *c, const unsigned char *handles) {
         cudaIpcMemHandle_t h;
         memcpy(&h, handles + (size_t)r * GA_IPC_HANDLE_BYTES, sizeof(h));
         void *ptr = nullptr;
-        CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+        cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            // leave nothing half-opened: a retry would map the earlier peers a second time
+            for (int q = 0; q < c->world; ++q) {
+                if (!c->peer_base[q]) continue;
+                cudaIpcCloseMemHandle(c->peer_base[q]);
+                c->peer_base[q] = nullptr; c->pad_all[q] = nullptr; c->send_all[q] = nullptr; c->gather_all[q] = nullptr;
+            }
+            return fail(GA_ECUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s", r, cudaGetErrorString(e));
+        }
         c->peer_base[r] = ptr;
         c->pad_all[r] = (Pad *)ptr;
         c->send_all[r] = (char *)ptr + kPadBytes;
@@ -1399,8 +1325,9 @@ int ga_open_peers(ga_ctx *c, const unsigned char *handles) {
     return GA_OK;
 }
 
-int ga_allreduce_tensors(ga_ctx *c, const void *const *ptrs, const int64_t *numel, int n_tensors,
-                         int op, void *stream, int variant) {
+namespace {
+int tensors_call(ga_ctx *c, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                 int op, void *stream, int variant, int root, int max_blocks) {
     if (!c) return fail(GA_EINVAL, "NULL context");
     if (n_tensors < 0 || (n_tensors > 0 && (!ptrs || !numel))) return fail(GA_EINVAL, "bad tensor list");
     uint64_t total = 0;
@@ -1432,10 +1359,30 @@ int ga_allreduce_tensors(ga_ctx *c, const void *const *ptrs, const int64_t *nume
             start += (uint32_t)tiles_for_elems(numel[i]);
         }
     }
-    rc = launch(c, segs, (uint32_t)n_tensors, (uint32_t)total, op, stream, variant, false);
+    rc = ga_order_stream(c, stream);
+    if (rc == GA_OK) rc = launch(c, segs, (uint32_t)n_tensors, (uint32_t)total, op, stream, variant, false, 0, root, max_blocks);
     if (segs != stack_segs) free(segs);
     return rc;
 }
+}  // namespace
+
+int ga_allreduce_tensors(ga_ctx *c, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                         int op, void *stream, int variant) {
+    return tensors_call(c, ptrs, numel, n_tensors, op, stream, variant, 0, 0);
+}
+
+int ga_allreduce_tensors_ex(ga_ctx *c, const void *const *ptrs, const int64_t *numel, int n_tensors,
+                            int op, void *stream, int variant, int max_blocks) {
+    if (max_blocks < 0) return fail(GA_EINVAL, "max_blocks is negative");
+    return tensors_call(c, ptrs, numel, n_tensors, op, stream, variant, 0, max_blocks);
+}
+
+int ga_broadcast_tensors(ga_ctx *c, const void *const *ptrs, const int64_t *numel, int n_tensors, int root, void *stream) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (root < 0 || root >= c->world) return fail(GA_EINVAL, "root=%d outside world=%d", root, c->world);
+    return tensors_call(c, ptrs, numel, n_tensors, GA_OP_F32_SUM, stream, kVariantBcast, root, 0);
+}
+
 
 int ga_average(ga_ctx *c, const void *const *grad_ptrs, const int64_t *numel, int n_tensors,
                void *stream, int variant) {
@@ -1447,6 +1394,8 @@ int ga_allreduce_bucket(ga_ctx *c, size_t nbytes, int op, void *stream, int vari
     if (nbytes > c->capacity_bytes) return fail(GA_ECAPACITY, "%zu bytes exceed the bucket capacity %zu", nbytes, c->capacity_bytes);
     if (nbytes % 4) return fail(GA_EINVAL, "nbytes must be a multiple of 4");
     const uint32_t tiles = (uint32_t)((nbytes + kTileBytes - 1) / kTileBytes);
+    const int rc = ga_order_stream(c, stream);
+    if (rc) return rc;
     return launch(c, nullptr, 0, tiles, op, stream, variant, true);
 }
 
@@ -1464,6 +1413,8 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
     ENTER_DEVICE(c->device);
     cudaStream_t st = (cudaStream_t)stream;
+    rc = ga_order_stream(c, stream);
+    if (rc) return rc;
     rc = drain_if_needed(c, stream);
     if (rc) return rc;
     const size_t bucket_bytes = (size_t)total * kTileBytes;
@@ -1514,6 +1465,8 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
 int ga_bucket_acquire(ga_ctx *c, void *stream) {
     if (!c) return fail(GA_EINVAL, "NULL context");
     if (c->broken) return fail(GA_ESTATE, "context is unusable after an earlier timeout");
+    const int rc = ga_order_stream(c, stream);
+    if (rc) return rc;
     return drain_if_needed(c, stream);
 }
 
@@ -1590,6 +1543,7 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
             c->host_chunk_bytes = value < (int64_t)kTileBytes ? kTileBytes : ((size_t)value + kTileBytes - 1) / kTileBytes * kTileBytes;
             return GA_OK;
         case GA_OPT_PIPE_GROUP: c->pipe_group_opt = value < 0 ? 0 : (value > 64 ? 64 : (int)value); return GA_OK;
+        case GA_OPT_VIEW_CHUNK_TILES: c->view_chunk_opt = value < 0 ? 0 : (value > 65536 ? 65536 : (int)value); return GA_OK;
     }
     return fail(GA_EINVAL, "unknown option %d", option);
 }
@@ -1637,6 +1591,7 @@ int ga_close_peers(ga_ctx *c) {
             c->gather_all[r] = nullptr;
         }
     }
+    ga_view_release(c, false);
     if (c->n_local != c->world) c->opened = false;
     return GA_OK;
 }
@@ -1645,6 +1600,8 @@ int ga_destroy(ga_ctx *c) {
     if (!c) return GA_OK;
     DeviceGuard device_guard_(c->device);
     cudaDeviceSynchronize();
+    ga_view_release(c, true);
+    if (c->order_event) cudaEventDestroy(c->order_event);
     for (int r = 0; r < c->world; ++r)
         if (c->peer_base[r]) cudaIpcCloseMemHandle(c->peer_base[r]);
     for (int l = 0; l < c->n_local; ++l) {
@@ -1680,15 +1637,16 @@ int ga_destroy(ga_ctx *c) {
 // synchronisation of cudaMalloc/cudaFree is unacceptable, and plug-in hosts that forbid
 // allocation after start-up.  ga_create cannot serve them: it cudaMallocs the bucket, the flag
 // pad and a pinned status word.  This entry point keeps all of that in one file-scope device
-// array instead, which the driver places when the library is loaded and which every GPU that
-// loads the library keeps until the process exits.
+// array instead.  The array is part of the library's device image: with CUDA's default lazy module
+// loading the driver reserves its 8.53 MiB on a GPU the first time the library touches that GPU
+// (the first call below), and the GPU then keeps it until the process exits.
 namespace {
 
 constexpr size_t kStaticBucketBytes = (size_t)8 << 20;    // bucket space shared by ALL hosted ranks
-constexpr size_t kStaticStatusBytes = 256;
 constexpr size_t kStaticPadsBytes = kMaxWorld * kPadBytes;
-constexpr size_t kStaticBytes = kStaticPadsBytes + kStaticStatusBytes + kStaticBucketBytes;
+constexpr size_t kStaticBytes = kStaticPadsBytes + kStaticBucketBytes;      // 8 945 664 bytes
 constexpr int kStaticMaxDevices = 64;
+static_assert(sizeof(((Pad *)0)->reserved) >= sizeof(int), "the status word lives in the pad's spare words");
 
 // In host code this name is only a handle for cudaGetSymbolAddress, never an address to pass on.
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticBytes];
@@ -1700,6 +1658,29 @@ struct StaticDevice {
     int blocks_per_sm[2][kMaxWorld + 1];
 };
 StaticDevice g_static_dev[kStaticMaxDevices];
+
+unsigned long long static_timeout_ns() {
+    static unsigned long long ns = [] {
+        const char *env = getenv("GA_TIMEOUT_MS");           // the same knob the contexts read
+        return env ? strtoull(env, nullptr, 10) * 1000000ull : 30ull * 1000000000ull;
+    }();
+    return ns;
+}
+
+// Once per device, with that device current: the array's address ON THIS DEVICE.
+int static_setup(int device, StaticDevice **out) {
+    StaticDevice &sd = g_static_dev[device];
+    if (!sd.ready) {
+        void *addr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&addr, g_static_scratch));
+        if (!addr) return fail(GA_ECUDA, "cudaGetSymbolAddress returned a null address");
+        CUDA_TRY(cudaDeviceGetAttribute(&sd.sm_count, cudaDevAttrMultiProcessorCount, device));
+        sd.scratch = (unsigned char *)addr;
+        sd.ready = true;
+    }
+    *out = &sd;
+    return GA_OK;
+}
 
 }  // namespace
 
@@ -1724,31 +1705,21 @@ extern "C" int ga_average_static(int world, int device, const void *const *grad_
     if (variant != GA_VARIANT_ONESHOT && variant != GA_VARIANT_TWOSHOT) return fail(GA_EINVAL, "unknown variant %d", variant);
 
     ENTER_DEVICE(device);
-    StaticDevice &sd = g_static_dev[device];
-    if (!sd.ready) {
-        // Once per device, with that device current: resolve the array's address ON THIS DEVICE.
-        void *addr = nullptr;
-        CUDA_TRY(cudaGetSymbolAddress(&addr, g_static_scratch));
-        if (!addr) return fail(GA_ECUDA, "cudaGetSymbolAddress returned a null address");
-        CUDA_TRY(cudaDeviceGetAttribute(&sd.sm_count, cudaDevAttrMultiProcessorCount, device));
-        sd.scratch = (unsigned char *)addr;
-        sd.ready = true;
-    }
+    StaticDevice *sdp = nullptr;
+    rc = static_setup(device, &sdp);
+    if (rc) return rc;
+    StaticDevice &sd = *sdp;
     cudaStream_t st = (cudaStream_t)stream;
-    // The array still holds the previous call's flags: everything the protocol counts from zero
-    // (flag rows, done words, block counter, status) is cleared on the stream before each launch.
-    CUDA_TRY(cudaMemsetAsync(sd.scratch, 0, (size_t)world * kPadBytes, st));
-    CUDA_TRY(cudaMemsetAsync(sd.scratch + kStaticPadsBytes, 0, kStaticStatusBytes, st));
 
     Params p;
     memset(&p, 0, sizeof(p));
     const size_t per_rank = (size_t)total * kTileBytes;
     for (int r = 0; r < world; ++r) {
         p.pad[r] = (Pad *)(sd.scratch + (size_t)r * kPadBytes);
-        p.send[r] = sd.scratch + kStaticPadsBytes + kStaticStatusBytes + (size_t)r * per_rank;
+        p.send[r] = sd.scratch + kStaticPadsBytes + (size_t)r * per_rank;
     }
-    p.status = (int *)(sd.scratch + kStaticPadsBytes);
-    p.timeout_ns = 30ull * 1000000000ull;
+    p.status = (int *)(sd.scratch + offsetof(Pad, reserved));      // rank 0's spare pad words: read back by ga_static_status
+    p.timeout_ns = static_timeout_ns();
     p.n_seg = (uint32_t)n_tensors;
     p.total_tiles = (uint32_t)total;
     p.shard_tiles = ((uint32_t)total + world - 1) / world;
@@ -1781,9 +1752,38 @@ extern "C" int ga_average_static(int world, int device, const void *const *grad_
     if (resident < 1) resident = 1;
     int blocks = (int)((slots + wpb - 1) / wpb);
     if (blocks > resident) blocks = resident;
+
+    // The array still holds the previous call's flags.  What the protocol counts up from zero is
+    // cleared on the stream before the launch, and only that: the flag rows of the blocks this launch
+    // uses and the tail of each pad (done words, block counter, epoch, status) -- a few KB per rank in
+    // three strided memsets, whatever the world size.
+    unsigned char *pad0 = sd.scratch;
+    const size_t rows = (size_t)blocks * kMaxWorld * sizeof(uint32_t);
+    CUDA_TRY(cudaMemset2DAsync(pad0 + offsetof(Pad, ready), kPadBytes, 0, rows, (size_t)world, st));
+    if (variant == GA_VARIANT_TWOSHOT)
+        CUDA_TRY(cudaMemset2DAsync(pad0 + offsetof(Pad, mid), kPadBytes, 0, rows, (size_t)world, st));
+    CUDA_TRY(cudaMemset2DAsync(pad0 + offsetof(Pad, done), kPadBytes, 0, sizeof(Pad) - offsetof(Pad, done), (size_t)world, st));
+
     dim3 grid(blocks, world), block(kThreads);
     void *args[] = {&p};
     if (world > 1) CUDA_TRY(cudaLaunchCooperativeKernel((const void *)fn, grid, block, args, 0, st));
     else CUDA_TRY(cudaLaunchKernel((const void *)fn, grid, block, args, 0, st));
+    return GA_OK;
+}
+
+// Outcome of the ga_average_static calls enqueued on `stream` so far, for callers that cannot
+// allocate either: waits for the stream, then copies the one status word out of the device array
+// into a stack variable.  GA_OK, or GA_ETIMEOUT if a block of the last call gave up waiting for a flag
+// (its gradients are then only partly averaged).
+extern "C" int ga_static_status(int device, void *stream) {
+    if (device < 0 || device >= kStaticMaxDevices) return fail(GA_EINVAL, "device=%d outside 0..%d", device, kStaticMaxDevices - 1);
+    ENTER_DEVICE(device);
+    StaticDevice *sd = nullptr;
+    int rc = static_setup(device, &sd);
+    if (rc) return rc;
+    CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+    int word = 0;
+    CUDA_TRY(cudaMemcpy(&word, sd->scratch + offsetof(Pad, reserved), sizeof word, cudaMemcpyDeviceToHost));
+    if (word != 0) return fail(word, "a ga_average_static kernel timed out waiting for a flag: its gradients are only partly averaged");
     return GA_OK;
 }

@@ -13,6 +13,9 @@ Names the reference touches and what they do here:
                       kernel (one-tensor bucket); other ops/dtypes are rejected, not routed elsewhere
   reduce_op/ReduceOp  mnist/main.py:126, toy/main.py:20
   new_group           toy/main.py:16                            the all-ranks group is a cheap token
+  broadcast           (absent from the reference, which relies on identical seeds it never sets,
+                      mnist/main.py:185)                        rank `src`'s tensor into every rank's, over the
+                      same peer mappings
 Everything else resolves to `torch.distributed` unchanged.
 """
 import os
@@ -81,6 +84,23 @@ def all_reduce(tensor, op=_td.ReduceOp.SUM, group=None, async_op=False):
     staged = tensor.to(avg.device, non_blocking=False).contiguous()
     avg.all_reduce_([[staged]])
     tensor.copy_(staged)            # synchronises: the call is blocking, as on gloo
+    return None
+
+
+def broadcast(tensor, src=0, group=None, async_op=False):
+    """In-place broadcast of rank `src`'s tensor (the initial-parameter sync the reference lacks)."""
+    from .averager import default_averager
+    if async_op:
+        raise GradAvgError(_lib.GA_EINVAL, "async_op=True is not supported on this path")
+    if group is not None and not isinstance(group, WorldToken):
+        raise GradAvgError(_lib.GA_EINVAL, "only the default / all-ranks group is supported")
+    avg = default_averager()
+    if tensor.is_cuda:
+        avg.broadcast_([[tensor]], root=src)
+        return None
+    staged = tensor.to(avg.device).contiguous()
+    avg.broadcast_([[staged]], root=src)
+    tensor.copy_(staged)
     return None
 
 

@@ -155,7 +155,7 @@ def test_plan_cache_survives_id_reuse():
     avg._lib, avg._ctx, avg._lock = FakeLib(), ctypes.c_void_p(1), threading.Lock()
     avg._variant, avg._capacity, avg._local, avg.world_size, avg.rank = 0, 1 << 30, 0, 2, 0
     avg._device, avg._dev_obj, avg._plans, avg._ptr_cache, avg._group = 0, torch.device("cuda", 0), {}, {}, None
-    avg._launch_base = 0
+    avg._launch_base, avg._adopted = 0, None
     orig = averager.torch.cuda.current_stream
     averager.torch.cuda.current_stream = lambda d=None: type("S", (), {"cuda_stream": 0})()
     try:

@@ -1,12 +1,14 @@
-"""GPU: the allocation-free entry point `ga_average_static` against `ga_average`.
+"""GPU: the allocation-free entry point `ga_average_static` against `ga_average` and the oracle.
 
 Some users of this library may not call cudaMalloc when they need an average (their host
 application owns the allocator, or they sit in a section where cudaMalloc's implicit device
 synchronisation is not acceptable), so `ga_average_static` keeps its bucket and flags in an
 array built into the library.  This file checks, through the C ABI, that it returns the same
-bytes as the context-based call on the same inputs -- the tolerance is zero, as everywhere in
-these tests -- twice in a row (the second call finds the first call's leftovers in the array),
-and that it refuses gradient sets larger than the built-in array.  It is named so that pytest
+bytes as the context-based call on the same inputs and as oracle/fold.c -- the tolerance is zero,
+as everywhere in these tests -- twice in a row (the second call finds the first call's leftovers in
+the array), that its outcome can be read back without allocating (`ga_static_status`), that no
+device memory is taken after the first call, and that it refuses gradient sets larger than the
+built-in array.  It is named so that pytest
 collects it last; it must pass alone in a fresh process as well as after the whole suite.
 """
 import ctypes
@@ -48,6 +50,10 @@ def _static(lib, world, per_rank, variant):
     assert lib.ga_average_static(world, 0, ptrs, numel, n, st, variant) == 0, lib.ga_last_error()
 
 
+def _oracle(host, world):
+    return [oracle.fold_average_c([host[r][i].numpy() for r in range(world)]) for i in range(len(host[0]))]
+
+
 def test_static_matches_context_call_twice_in_a_row(built):
     lib = built
     torch.cuda.set_device(0)
@@ -71,9 +77,12 @@ def test_static_matches_context_call_twice_in_a_row(built):
                 for a, b in zip(again_got[r], again_want[r]):
                     assert torch.equal(a, b) and a.cpu().numpy().tobytes() == b.cpu().numpy().tobytes()
         torch.cuda.synchronize()
+        assert lib.ga_static_status(0, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)) == 0, lib.ga_last_error()
+        folded = _oracle(host, world)
         for r in range(world):
-            for a, b in zip(got[r], want[r]):
+            for a, b, c in zip(got[r], want[r], folded):
                 assert a.cpu().numpy().tobytes() == b.cpu().numpy().tobytes(), "call %d rank %d" % (call, r)
+                assert a.cpu().numpy().tobytes() == c.tobytes(), "call %d rank %d vs oracle/fold.c" % (call, r)
     # a different world size afterwards reuses the same array from a different layout
     for world in (2, 8, 1):
         host = [oracle.seeded_grads(oracle.MINI_SHAPES, r) for r in range(world)]
@@ -85,6 +94,29 @@ def test_static_matches_context_call_twice_in_a_row(built):
         for r in range(world):
             for a, b in zip(got[r], want[r]):
                 assert a.cpu().numpy().tobytes() == b.cpu().numpy().tobytes()
+
+
+def test_static_takes_no_device_memory_after_its_first_call(built):
+    """The array is reserved when the library's device code is first used on the GPU; later calls
+    must leave cudaMemGetInfo's free figure where it was."""
+    lib = built
+    torch.cuda.set_device(0)
+    world = 2
+    host = [oracle.seeded_grads(oracle.MINI_SHAPES, r) for r in range(world)]
+    dev = [[t.cuda() for t in rank] for rank in host]
+    _static(lib, world, dev, TWOSHOT)                       # first use on this device (if the other tests did not run)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info(0)
+    for variant in (ONESHOT, TWOSHOT, ONESHOT):
+        dev = [[t.cuda() for t in rank] for rank in host]   # torch's cached blocks: no new cudaMalloc
+        _static(lib, world, dev, variant)
+        assert lib.ga_static_status(0, None) == 0
+    free1, _ = torch.cuda.mem_get_info(0)
+    assert free1 == free0
+    want = _oracle(host, world)
+    for r in range(world):
+        for a, w in zip(dev[r], want):
+            assert a.cpu().numpy().tobytes() == w.tobytes()
 
 
 def test_static_rejects_what_does_not_fit(built):
