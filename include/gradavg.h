@@ -92,6 +92,10 @@ extern "C" {
 #define GA_OPT_HOST_CHUNK_BYTES  5   /* ga_average_host: largest chunk of the copy-in / reduce / copy-out pipeline */
 #define GA_OPT_PIPE_GROUP        4   /* TWOSHOT_PIPE: tile slots per block per round (0 = automatic) */
 #define GA_OPT_VIEW_CHUNK_TILES  7   /* GA_VARIANT_VIEW: 2 KiB tiles per chunk (0 = automatic) */
+#define GA_OPT_VIEW_ONESHOT_MAX_BYTES 8 /* GA_VARIANT_VIEW: sets up to this size take the one-shot form (every rank receives
+                                        every tile, folds all of it locally); -1 = automatic, 0 = never */
+#define GA_OPT_VIEW_MIN_BYTES    9   /* ga_average_view with GA_VARIANT_AUTO: smaller sets go through the bucket kernels
+                                        (region = one tensor), larger ones through the in-place kernel (default 32 MiB) */
 
 /* flags for ga_view_create */
 #define GA_VIEW_MULTICAST        1   /* also map the regions through an NVSwitch multicast object when the GPUs
@@ -224,7 +228,9 @@ int ga_multicast_supported(int device);
  * Trainer.average_gradients (mnist/main.py:122-127) IN PLACE on the first `nbytes` of every rank's
  * view region: afterwards every rank's region holds the rank-order sum divided by (float)world
  * (GA_OP_F32_AVG; the other ops as in ga_allreduce_tensors).  One kernel on `stream`, asynchronous.
- * variant: GA_VARIANT_AUTO / GA_VARIANT_VIEW (bit-exact) or GA_VARIANT_NVLS (opt-in, see above).
+ * variant: GA_VARIANT_VIEW (the in-place kernel), GA_VARIANT_AUTO (that kernel from GA_OPT_VIEW_MIN_BYTES on,
+ * below it the bucket kernels with the region as their one tensor: same bits, quicker for small sets)
+ * or GA_VARIANT_NVLS (opt-in, see above).
  * This is also the same-buffer form to time against NCCL all_reduce, which is in place too.
  */
 int ga_average_view(ga_ctx *ctx, size_t nbytes, int op, void *stream, int variant);

@@ -15,6 +15,8 @@ OPT_ONESHOT_MAX_BYTES, OPT_TIMEOUT_MS, OPT_MAX_BLOCKS, OPT_PIPE_GROUP = 1, 2, 3,
 OPT_HOST_CHUNK_BYTES = 5
 OPT_TRACE = 6
 OPT_VIEW_CHUNK_TILES = 7
+OPT_VIEW_ONESHOT_MAX_BYTES = 8
+OPT_VIEW_MIN_BYTES = 9
 VIEW_MULTICAST = 1
 VIEW_HANDLE_BYTES = 128
 IPC_HANDLE_BYTES = 64

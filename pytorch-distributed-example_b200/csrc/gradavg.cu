@@ -969,6 +969,8 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     set_auto_thresholds(c);
     c->timeout_ns = 30ull * 1000000000ull;
     c->host_chunk_bytes = (size_t)8 << 20;
+    c->view_oneshot_max_opt = -1;
+    c->view_min_bytes = (size_t)32 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
     if (env) c->timeout_ns = strtoull(env, nullptr, 10) * 1000000ull;
     const int rc = create_body(c, device);
@@ -1544,6 +1546,8 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
             return GA_OK;
         case GA_OPT_PIPE_GROUP: c->pipe_group_opt = value < 0 ? 0 : (value > 64 ? 64 : (int)value); return GA_OK;
         case GA_OPT_VIEW_CHUNK_TILES: c->view_chunk_opt = value < 0 ? 0 : (value > 65536 ? 65536 : (int)value); return GA_OK;
+        case GA_OPT_VIEW_ONESHOT_MAX_BYTES: c->view_oneshot_max_opt = value < 0 ? -1 : (long long)value; return GA_OK;
+        case GA_OPT_VIEW_MIN_BYTES: c->view_min_bytes = value < 0 ? 0 : (size_t)value; return GA_OK;
     }
     return fail(GA_EINVAL, "unknown option %d", option);
 }

@@ -256,6 +256,8 @@ struct ga_ctx {
     int view_fd, view_mc_fd;                // descriptors exported to the peers, closed by ga_view_bind
     bool view_opened, view_mc_added, view_mc_bound;
     int view_chunk_opt;                     // GA_OPT_VIEW_CHUNK_TILES (0 = automatic)
+    long long view_oneshot_max_opt;         // GA_OPT_VIEW_ONESHOT_MAX_BYTES (-1 = automatic)
+    size_t view_min_bytes;                  // GA_OPT_VIEW_MIN_BYTES: AUTO uses the in-place kernel from this size on
 };
 
 // stream ordering between consecutive launches of one context (gradavg.cu)

@@ -42,6 +42,7 @@ struct ViewParams {
     uint32_t n_chunks;          // chunks per shard, <= kMaxBlocks
     int rank_base;
     int world;                  // ga_nvls_kernel: runtime world size
+    int oneshot;                // ga_view_kernel: 1 = every rank receives every tile and folds everything locally
 };
 
 template <int OP, int N>
@@ -61,88 +62,207 @@ __device__ __forceinline__ Vec fold_vecs(const Vec (&v)[N], float wf) {
     return acc;
 }
 
-// Trace slots: 0 start, 1 previous launch's staging released (scatter) / -, 2 all chunks issued,
-// 3 last flags raised, 4 (fold) every peer's results seen, 9 end.
+// phase timestamp written by whichever single thread calls it (GA_TRACE is thread 0 only)
+template <typename P> __device__ __forceinline__ void trace_at(const P &p, int slot) {
+    if (p.trace) p.trace[((size_t)blockIdx.y * gridDim.x + blockIdx.x) * kTraceSlots + slot] = global_ns();
+}
+
+constexpr uint32_t kRing = 16;     // chunk ordinals a block's data warps may run ahead of its control warp
+
+__device__ __forceinline__ uint32_t ld_vol(const uint32_t *p) { return *(const volatile uint32_t *)p; }
+__device__ __forceinline__ void st_vol(uint32_t *p, uint32_t v) { *(volatile uint32_t *)p = v; }
+
+// Two warps of every block are CONTROL warps, one thread each: warp 1 is the PUBLISHER (waits until the
+// data warps have issued a chunk, pays the system-scope fence, raises the chunk's flags in every
+// rank's pad); in fold blocks warp 0 is the POLLER (waits for a chunk's flags from every rank, then
+// releases it to the data warps).  The other warps are DATA warps that stream through the block's
+// chunks and never wait for a fence: they tick a shared-memory counter per finished chunk.  Measured
+// (profiles/r02_*): with the whole block behind one barrier per chunk, or with one control thread
+// doing both jobs, a fence -- 40-50 us when the links are busy, it waits for the queue in front of it
+// -- stood between a block and its next chunk, and more than one round per block made the kernel
+// slower.  A fence by one thread does not slow the other warps' stores (nvlink_probe st16_fence).
+//
+// Trace slots (even blocks scatter, odd blocks fold): 0 start; 1 staging released by the previous
+// launch's owners (scatter); 3 first chunk's flags raised (scatter) / first chunk arrived (fold);
+// 5 a data warp has issued its last chunk; 6 last chunk arrived (fold); 2 last flags raised;
+// 4 every peer's results seen (fold); 9 end.
 template <int W, int OP>
 __global__ void __launch_bounds__(kThreads, 2) ga_view_kernel(const __grid_constant__ ViewParams p) {
     __shared__ int s_abort;
     __shared__ int s_last;
+    __shared__ uint32_t s_cnt[kRing];      // data warps that have finished chunk ordinal q (slot q % kRing)
+    __shared__ uint32_t s_sig;             // ordinals whose flags the publisher has raised (frees ring slots)
+    __shared__ uint32_t s_ready;           // fold blocks: ordinals whose inputs have arrived from every rank
     const int ly = blockIdx.y;
     const int r = p.rank_base + ly;
     const int lane = threadIdx.x & 31;
     const uint32_t warp = threadIdx.x >> 5;
-    const uint32_t wpb = blockDim.x >> 5;
     const uint32_t T = p.total_tiles, Ts = p.shard_tiles, C = p.chunk_tiles, NC = p.n_chunks;
     const uint32_t k = blockIdx.x >> 1, nb = gridDim.x >> 1;     // index / count within my role
+    const uint32_t nq = NC > k ? (NC - k + nb - 1) / nb : 0;      // my chunks: c = k + q * nb, q = 0 .. nq-1
     const bool scatter_role = (blockIdx.x & 1u) == 0;
+    // scatter blocks: warp 1 publishes, warps 0, 2..15 move data; fold blocks: warp 0 polls, warp 1 publishes, 2..15 fold
+    const uint32_t ndata = (blockDim.x >> 5) - (scatter_role ? 1u : 2u);
+    const uint32_t dw = scatter_role ? (warp == 0 ? 0u : warp - 1) : warp - 2;   // data-warp index (control warps never use it)
     const float wf = (float)W;
 
     Pad *mypad = p.pad[r];
     const uint32_t epoch = ld_relaxed_sys(&mypad->epoch) + 1;    // same value in every block of this launch
-    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; }
+    if (threadIdx.x < kRing) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) { s_abort = 0; s_last = 0; s_sig = 0; s_ready = 0; }
     __syncthreads();
     GA_TRACE(p, 0);
+
+    // data warp: this warp's part of chunk ordinal q is issued
+    auto finish = [&](uint32_t q) {
+        __syncwarp();
+        if (lane == 0) { __threadfence_block(); atomicAdd(&s_cnt[q % kRing], 1u); }
+    };
+    // data warp: ring slot of ordinal q is free again
+    auto ring_wait = [&](uint32_t q) {
+        if (q >= kRing) {
+            if (lane == 0) while (ld_vol(&s_sig) + kRing <= q && *(volatile int *)&s_abort == 0) {}
+            __syncwarp();
+        }
+    };
+    // publisher thread: as the data warps finish chunk ordinal q -> fence, raise `row`[c][r] in every pad
+    auto publisher = [&](size_t row_off, bool raise) {
+        for (uint32_t q = 0; q < nq; ++q) {
+            while (ld_vol(&s_cnt[q % kRing]) < ndata) { if (*(volatile int *)&s_abort) return; }
+            st_vol(&s_cnt[q % kRing], 0);
+            if (raise) {
+                asm volatile("fence.acq_rel.sys;" ::: "memory");
+                const size_t off = row_off + (size_t)(k + q * nb) * kMaxWorld + r;
+#pragma unroll
+                for (int j = 0; j < W; ++j) st_relaxed_sys((uint32_t *)p.pad[j] + off, epoch);
+            }
+            st_vol(&s_sig, q + 1);
+            if (q == 0 && scatter_role) trace_at(p, 3);
+        }
+        trace_at(p, 2);
+    };
 
     if (scatter_role) {
         // the owners must have folded the previous launch's staging data before it is overwritten
         if (!wait_flags<W>(mypad->done, epoch - 1, p, &s_abort)) return;
         GA_TRACE(p, 1);
-        constexpr uint32_t kPeers = W > 1 ? W - 1 : 1;
-        for (uint32_t c = k; c < NC; c += nb) {
-            const uint32_t i0 = c * C;
-            if (W > 1) {
-                for (uint32_t it = warp; it < C * kPeers; it += wpb) {
-                    const uint32_t i = i0 + it / kPeers;
-                    const int j = (r + 1 + (int)(it % kPeers)) % W;           // nearest rank first: W ranks, W different destinations
-                    const uint32_t t = j * Ts + i;
-                    if (i >= Ts || t >= T) continue;
-                    const Vec *src = (const Vec *)p.view[r] + (size_t)t * kTileVecs + lane;
-                    Vec v[kLaneVecs];
+        if (warp == 1) {
+            if (lane == 0) publisher(offsetof(Pad, ready) / 4, true);
+        } else {
+            constexpr uint32_t kPeers = W > 1 ? W - 1 : 1;
+            for (uint32_t q = 0; q < nq; ++q) {
+                ring_wait(q);
+                const uint32_t i0 = (k + q * nb) * C;
+                if (W > 1 && p.oneshot) {
+                    // one-shot: tile t goes to EVERY peer, into the slot that peer keeps for me (T tiles per slot)
+                    for (uint32_t it = dw; it < C; it += ndata) {
+                        const uint32_t t = i0 + it;
+                        if (t >= T) continue;
+                        const Vec *src = (const Vec *)p.view[r] + (size_t)t * kTileVecs + lane;
+                        Vec v[kLaneVecs];
 #pragma unroll
-                    for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcs(src + u * 32);
-                    Vec *dst = (Vec *)p.stage[j] + ((size_t)r * Ts + i) * kTileVecs + lane;
+                        for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcs(src + u * 32);
+#pragma unroll 1
+                        for (int jj = 1; jj < W; ++jj) {
+                            const int j = (r + jj) % W;
+                            Vec *dst = (Vec *)p.stage[j] + ((size_t)(r < j ? r : r - 1) * T + t) * kTileVecs + lane;
 #pragma unroll
-                    for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+                            for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+                        }
+                    }
+                } else if (W > 1) {
+                    for (uint32_t it = dw; it < C * kPeers; it += ndata) {
+                        const uint32_t i = i0 + it / kPeers;
+                        const int j = (r + 1 + (int)(it % kPeers)) % W;       // nearest rank first: W ranks, W different destinations
+                        const uint32_t t = j * Ts + i;
+                        if (i >= Ts || t >= T) continue;
+                        const Vec *src = (const Vec *)p.view[r] + (size_t)t * kTileVecs + lane;
+                        Vec v[kLaneVecs];
+#pragma unroll
+                        for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcs(src + u * 32);
+                        Vec *dst = (Vec *)p.stage[j] + ((size_t)r * Ts + i) * kTileVecs + lane;
+#pragma unroll
+                        for (int u = 0; u < kLaneVecs; ++u) __stcg(dst + u * 32, v[u]);
+                    }
                 }
+                finish(q);
             }
-            raise_flags<W>(p, offsetof(Pad, ready) / 4 + (size_t)c * kMaxWorld + r, epoch);
+            if (warp == 0 && lane == 0) trace_at(p, 5);
         }
-        GA_TRACE(p, 2);
     } else {
-        const Vec *mystage = (const Vec *)p.stage[r];
-        for (uint32_t c = k; c < NC; c += nb) {
-            if (!wait_flags<W>(mypad->ready[c], epoch, p, &s_abort)) return;
-            const uint32_t i0 = c * C;
-            for (uint32_t it = warp; it < C * kLaneVecs; it += wpb) {
-                const uint32_t i = i0 + it / kLaneVecs;
-                const uint32_t t = r * Ts + i;
-                if (i >= Ts || t >= T) continue;
-                const size_t row = (size_t)(it % kLaneVecs) * 32 + lane;
-                Vec v[W];
-#pragma unroll
-                for (int s = 0; s < W; ++s) {
-                    const Vec *src = s == r ? (const Vec *)p.view[r] + (size_t)t * kTileVecs
-                                            : mystage + ((size_t)s * Ts + i) * kTileVecs;
-                    v[s] = __ldcg(src + row);
+        if (warp == 0) {
+            if (lane == 0) {
+                bool ok = true;
+                for (uint32_t q = 0; q < nq && ok; ++q) {
+                    const uint32_t *row = mypad->ready[k + q * nb];
+#pragma unroll 1
+                    for (int s = 0; s < W && ok; ++s) ok = spin_until(row + s, epoch, p.timeout_ns);
+                    if (!ok) break;
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");     // acquire: the ranks' chunk before the data warps' loads
+                    st_vol(&s_ready, q + 1);
+                    if (q == 0) trace_at(p, 3);
+                    if (q == nq - 1) trace_at(p, 6);
                 }
-                const Vec acc = fold_vecs<OP, W>(v, wf);
-#pragma unroll
-                for (int jj = 0; jj < W; ++jj) {
-                    const int j = (r + jj) % W;
-                    __stcg((Vec *)p.view[j] + (size_t)t * kTileVecs + row, acc);
+                // every rank's results for my chunks have landed in my region (block k of every rank owns
+                // the same chunks, so when all my blocks are through, all peers' blocks are); one-shot
+                // results are local, nothing to wait for
+                for (uint32_t q = 0; q < nq && ok && !p.oneshot; ++q) {
+                    const uint32_t *row = mypad->mid[k + q * nb];
+#pragma unroll 1
+                    for (int s = 0; s < W && ok; ++s) ok = spin_until(row + s, epoch, p.timeout_ns);
                 }
+                if (!ok) {
+                    *(volatile int *)p.status = GA_ETIMEOUT;
+                    *(volatile int *)&s_abort = 1;
+                } else {
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");
+                }
+                trace_at(p, 4);
             }
-            raise_flags<W>(p, offsetof(Pad, mid) / 4 + (size_t)c * kMaxWorld + r, epoch);
+        } else if (warp == 1) {
+            if (lane == 0) publisher(offsetof(Pad, mid) / 4, !p.oneshot);
+        } else {
+            const Vec *mystage = (const Vec *)p.stage[r];
+            const bool one = p.oneshot != 0;
+            for (uint32_t q = 0; q < nq; ++q) {
+                if (lane == 0) while (ld_vol(&s_ready) <= q && *(volatile int *)&s_abort == 0) {}
+                __syncwarp();
+                if (*(volatile int *)&s_abort) break;
+                __threadfence_block();
+                ring_wait(q);
+                const uint32_t i0 = (k + q * nb) * C;
+                for (uint32_t it = dw; it < C * kLaneVecs; it += ndata) {
+                    const uint32_t i = i0 + it / kLaneVecs;
+                    const uint32_t t = one ? i : r * Ts + i;                   // one-shot: chunks run over all T tiles
+                    if ((!one && i >= Ts) || t >= T) continue;
+                    const size_t row = (size_t)(it % kLaneVecs) * 32 + lane;
+                    Vec v[W];
+#pragma unroll
+                    for (int s = 0; s < W; ++s) {
+                        const Vec *src = s == r ? (const Vec *)p.view[r] + (size_t)t * kTileVecs
+                                         : one  ? mystage + ((size_t)(s < r ? s : s - 1) * T + t) * kTileVecs
+                                                : mystage + ((size_t)s * Ts + i) * kTileVecs;
+                        v[s] = __ldcg(src + row);
+                    }
+                    const Vec acc = fold_vecs<OP, W>(v, wf);
+                    if (one) {
+                        __stcg((Vec *)p.view[r] + (size_t)t * kTileVecs + row, acc);
+                    } else {
+#pragma unroll
+                        for (int jj = 0; jj < W; ++jj) {
+                            const int j = (r + jj) % W;
+                            __stcg((Vec *)p.view[j] + (size_t)t * kTileVecs + row, acc);
+                        }
+                    }
+                }
+                finish(q);
+            }
+            if (warp == 2 && lane == 0) trace_at(p, 5);
         }
-        GA_TRACE(p, 2);
-        // every rank's results for my chunks have landed in my region (block k of every rank owns the
-        // same chunks, so when all my blocks are through, all peers' blocks are)
-        for (uint32_t c = k; c < NC; c += nb)
-            if (!wait_flags<W>(mypad->mid[c], epoch, p, &s_abort)) return;
-        GA_TRACE(p, 4);
     }
 
     __syncthreads();
+    if (s_abort) return;
     if (threadIdx.x == 0) {
         __threadfence();
         s_last = atomicAdd(&mypad->finished_blocks, 1u) == gridDim.x - 1;
@@ -667,7 +787,18 @@ int ga_average_view(ga_ctx *c, size_t nbytes, int op, void *stream, int variant)
     if (op != GA_OP_F32_AVG && op != GA_OP_I32_SUM && op != GA_OP_F32_SUM) return fail(GA_EINVAL, "unknown op %d", op);
     if (nbytes % 4) return fail(GA_EINVAL, "nbytes must be a multiple of 4");
     if (nbytes > c->view_bytes) return fail(GA_ECAPACITY, "%zu bytes exceed the view region (%zu)", nbytes, c->view_bytes);
-    if (variant == GA_VARIANT_AUTO) variant = GA_VARIANT_VIEW;
+    if (variant == GA_VARIANT_AUTO) {
+        // Below ~32 MiB the bucket kernels are quicker even with their pack and unpack (their one-shot
+        // push skips the start-of-launch wait, profiles/r02_view_sweep_*): AUTO hands such sets to the
+        // tensor-list path with the region as its one tensor, and takes the in-place kernel from there on.
+        if (nbytes < c->view_min_bytes && c->world > 1) {
+            const void *ptrs[kMaxWorld];
+            for (int l = 0; l < c->n_local; ++l) ptrs[l] = c->view_own[l];
+            const int64_t numel = (int64_t)(nbytes / 4);
+            return ga_allreduce_tensors(c, ptrs, &numel, 1, op, stream, GA_VARIANT_AUTO);
+        }
+        variant = GA_VARIANT_VIEW;
+    }
     if (variant != GA_VARIANT_VIEW && variant != GA_VARIANT_NVLS) return fail(GA_EINVAL, "ga_average_view takes GA_VARIANT_VIEW or GA_VARIANT_NVLS, not %d", variant);
     if (variant == GA_VARIANT_NVLS && !c->view_mc)
         return fail(GA_ESTATE, "GA_VARIANT_NVLS needs a multicast mapping: create the view region with GA_VIEW_MULTICAST on a "
@@ -713,17 +844,33 @@ int ga_average_view(ga_ctx *c, size_t nbytes, int op, void *stream, int variant)
         if (blocks > resident) blocks = resident;
         if (blocks < 1) blocks = 1;
     } else {
-        // scatter and fold blocks in pairs; chunks sized so that every block of a role gets the same
-        // number of them (`rounds` each), small sets spread one chunk per block
+        // One-shot (every rank sends its whole region to every peer, folds everything locally, one
+        // flag round): same link bytes as two-shot at world 2, and one barrier less for small sets.
+        const size_t set_bytes = (size_t)tiles * kTileBytes;
+        // (N = 2 / 4 sweeps: one-shot wins up to 4 MiB / 1 MiB; beyond, its local fold no longer hides behind the transfer)
+        const size_t one_max = c->view_oneshot_max_opt >= 0 ? (size_t)c->view_oneshot_max_opt
+                                                            : ((size_t)4 << 20) / (size_t)(c->world > 1 ? c->world - 1 : 1);
+        p.oneshot = c->world > 1 && set_bytes <= one_max && set_bytes * (size_t)(c->world - 1) <= c->capacity_bytes;
+        // Scatter and fold blocks in pairs.  Chunk policy from the N = 2/4/8 sweeps (profiles/r02_view_sweep_*):
+        // the links are the limit and a chunk's flag only arrives after the queue in front of it has
+        // drained, so finer chunks do not start the fold any earlier -- large sets take one round of up
+        // to 64 tiles per block on every SM, mid sizes run on half the SMs with fuller blocks, small
+        // sets on at most 32 blocks of >= 4 tiles (more blocks only add flag traffic).
         if (resident < 2) resident = 2;
         const uint32_t nb_max = (uint32_t)resident / 2;
-        const uint32_t Ts = p.shard_tiles;
+        const uint32_t Ts = p.oneshot ? tiles : p.shard_tiles;     // tiles the chunks of one rank run over
         uint32_t chunk = (uint32_t)c->view_chunk_opt;
         if (chunk == 0) {
-            uint32_t rounds = (Ts + nb_max * 8 - 1) / (nb_max * 8);        // aim at ~8 tiles (16 KiB per destination) per chunk
-            if (rounds < 1) rounds = 1;
-            chunk = (Ts + nb_max * rounds - 1) / (nb_max * rounds);
-            if (chunk < 1) chunk = 1;
+            const uint32_t nb_half = nb_max > 1 ? nb_max / 2 : 1;
+            if (Ts <= 1024) {
+                chunk = (Ts + 31) / 32;
+                if (chunk < 4) chunk = 4;
+            } else if (Ts < nb_max * 32) {
+                chunk = (Ts + nb_half - 1) / nb_half;
+            } else {
+                const uint32_t rounds = (Ts + nb_max * 64 - 1) / (nb_max * 64);
+                chunk = (Ts + nb_max * rounds - 1) / (nb_max * rounds);
+            }
         }
         while ((Ts + chunk - 1) / chunk > (uint32_t)kMaxBlocks) ++chunk;     // one flag row per chunk
         p.chunk_tiles = chunk;

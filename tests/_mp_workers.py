@@ -149,9 +149,112 @@ def ipc_world(rank, world, port, q, backend):
             if pa.grad.cpu().numpy().tobytes() != pb.grad.cpu().numpy().tobytes():
                 out["fail"].append("overlap != after-backward")
                 break
+        note("part 5 done")
+        # 6. gradients as views of the peer-mapped region: in place, bit-exact; with NVSwitch multicast
+        #    where the GPUs have it (cuMem allocation + descriptors fetched with pidfd_getfd), else CUDA-IPC
+        nview = 3 * 431080 + 7
+        avg.create_view(8 << 20, multicast=True)
+        out["multicast"] = avg.has_multicast
+        rng6 = np.random.default_rng(6)
+        allh = [rng6.standard_normal(nview).astype(np.float32) for _ in range(world)]
+        want6 = oracle.fold_average_c(allh)
+        for rep, chunk in enumerate((0, 1, 5, 0)):
+            avg.set_option(_lib.OPT_VIEW_CHUNK_TILES, chunk)
+            if rank == rep % world:
+                torch.cuda._sleep(2_000_000)                    # launch skew
+            v = avg.view_tensor(nview * 4)
+            v.copy_(torch.from_numpy(allh[rank]))
+            avg.allreduce_view(nview * 4, variant="view")
+            avg.check_status()
+            if v.cpu().numpy().tobytes() != want6.tobytes():
+                out["fail"].append("view in place, chunk %d" % chunk)
+        # view calls alternating with tensor-list calls (shared staging and epoch), no host sync in between
+        keep6 = []
+        for step in range(40):
+            n6 = (70001, 5, 431080, 1 << 20)[step % 4]
+            g = torch.Generator(device="cuda").manual_seed(20_000 * step + rank)
+            x = torch.randn(n6, device="cuda", generator=g)
+            if step % 2 == 0:
+                v = avg.view_tensor(n6 * 4)
+                v.copy_(x)
+                avg.allreduce_view(n6 * 4)
+                res = v.clone()
+            else:
+                res = x.clone()
+                avg.all_reduce_([[res]], average=True, variant=("twoshot_pipe", "oneshot_push", "twoshot_push")[step % 3])
+            keep6.append((step, x, res))
+        avg.check_status()
+        for step, x, res in keep6:
+            gathered = [torch.empty_like(x) for _ in range(world)]
+            if backend == "gloo":
+                gathered = [torch.empty_like(x.cpu()) for _ in range(world)]
+                tdist.all_gather(gathered, x.cpu())
+            else:
+                tdist.all_gather(gathered, x)
+            if res.cpu().numpy().tobytes() != oracle.fold_average_c([t.cpu().numpy() for t in gathered]).tobytes():
+                out["fail"].append("view/tensor mix step %d" % step)
+        note("part 6 done (multicast=%s)" % out["multicast"])
+        # 7. opt-in in-switch variant: the switch's wide sum rounded once, then the division -- checked
+        #    against its own oracle (fold.c: oracle_fold_wide_average_f32), never against the rank-order fold
+        if avg.has_multicast:
+            v = avg.view_tensor(nview * 4)
+            for rep in range(3):
+                v.copy_(torch.from_numpy(allh[rank]))
+                avg.allreduce_view(nview * 4, variant="nvls")
+                avg.check_status()
+                got = v.cpu().numpy()
+                wide = oracle.fold_wide_average_c(allh)
+                same = float((got.view(np.uint32) == wide.view(np.uint32)).mean())
+                ulp = int(np.abs(got.view(np.int32).astype(np.int64) - wide.view(np.int32).astype(np.int64)).max())
+                scale = np.mean([np.abs(h) for h in allh], axis=0)
+                nerr = float((np.abs(got - want6) / np.maximum(scale, 1e-30)).max())
+                out["nvls"] = {"equal_to_wide_oracle": same, "max_ulp": ulp, "max_err_vs_rank_order_over_mean_abs": nerr}
+                if same < 1.0 or nerr > 1e-6:
+                    out["fail"].append("nvls: %s" % out["nvls"])
+            gathered = [torch.empty_like(v) for _ in range(world)]
+            tdist.all_gather(gathered, v) if backend != "gloo" else None
+            if backend != "gloo" and any(not torch.equal(gathered[0], t) for t in gathered):
+                out["fail"].append("nvls: ranks differ")
+        note("part 7 done")
+        # 8. parameter broadcast from a non-zero root, then adopt(): gradients live in the view region
+        torch.manual_seed(1000 + rank)                                # replicas differ, as in the reference
+        net = torch.nn.Sequential(torch.nn.Linear(37, 101), torch.nn.ReLU(), torch.nn.Linear(101, 10)).cuda()
+        root = world - 1
+        avg.broadcast_parameters(net, root=root)
+        avg.check_status()
+        torch.manual_seed(1000 + root)
+        ref = torch.nn.Sequential(torch.nn.Linear(37, 101), torch.nn.ReLU(), torch.nn.Linear(101, 10))
+        for p, q_ in zip(net.parameters(), ref.parameters()):
+            if p.detach().cpu().numpy().tobytes() != q_.detach().numpy().tobytes():
+                out["fail"].append("broadcast: parameter differs from the root's")
         out["launches"] = avg.launch_count
         tdist.barrier()
         ga.reset_default_averager()
+        # adopt() on a fresh averager (a context holds one view region)
+        avg2 = ga.GradAverager(capacity_bytes=4 << 20)
+        opt = torch.optim.SGD(net.parameters(), lr=0.1)
+        avg2.adopt(net, optimizer=opt)
+        for step in range(3):
+            opt.zero_grad()                                           # set_to_none=False through adopt(optimizer=)
+            xg = torch.Generator(device="cuda").manual_seed(50 + 10 * step + rank)
+            net(torch.randn(8, 37, device="cuda", generator=xg)).square().mean().backward()
+            before = [p.grad.clone() for p in net.parameters()]
+            avg2.average_gradients(net.parameters())
+            avg2.check_status()
+            for i, (b, p) in enumerate(zip(before, net.parameters())):
+                gathered = [torch.empty_like(b.cpu()) for _ in range(world)]
+                tdist.all_gather(gathered, b.cpu()) if backend == "gloo" else None
+                if backend != "gloo":
+                    gathered = [torch.empty_like(b) for _ in range(world)]
+                    tdist.all_gather(gathered, b)
+                if p.grad.cpu().numpy().tobytes() != oracle.fold_average_c([t.cpu().numpy().ravel() for t in gathered]).tobytes():
+                    out["fail"].append("adopt step %d tensor %d" % (step, i))
+            opt.step()
+        if avg2._adopted is None or any(p.grad.data_ptr() != a for p, a in zip(net.parameters(), avg2._adopted[1])):
+            out["fail"].append("adopt: gradients left their views")
+        out["launches"] += avg2.launch_count
+        tdist.barrier()
+        avg2.close()
         tdist.destroy_process_group()
     except Exception as e:                                    # report, never hang the parent
         import traceback

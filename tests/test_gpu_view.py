@@ -38,8 +38,11 @@ def test_view_region_in_place_is_bit_exact(built, world):
             return torch.as_tensor(h, device="cuda:0")
 
         rng = np.random.default_rng(7)
-        for n, chunk in ((1, 0), (511, 0), (512 * 37 + 5, 1), (431080, 0), (431080, 3), (1_400_003, 0), (1_400_003, 64), (cap // 4, 0)):
-            assert lib.ga_set_option(ctx, 7, chunk) == 0
+        # (elements, chunk tiles [0 = automatic], one-shot limit [-1 = automatic, 0 = two-shot only, big = one-shot only])
+        cases = ((1, 0, -1), (511, 0, 0), (512 * 37 + 5, 1, -1), (512 * 37 + 5, 2, 1 << 40), (431080, 0, -1), (431080, 3, 0),
+                 (431080, 5, 1 << 40), (1_400_003, 0, -1), (1_400_003, 64, 0), (cap // 4 // max(1, world - 1), 0, 1 << 40), (cap // 4, 0, -1))
+        for n, chunk, one in cases:
+            assert lib.ga_set_option(ctx, 7, chunk) == 0 and lib.ga_set_option(ctx, 8, one) == 0
             host = [rng.standard_normal(n).astype(np.float32) for _ in range(world)]
             for l in range(world):
                 view(l, n).copy_(torch.from_numpy(host[l]))
@@ -48,8 +51,8 @@ def test_view_region_in_place_is_bit_exact(built, world):
             assert lib.ga_status(ctx) == 0
             want = _fold(host)
             for l in range(world):
-                assert view(l, n).cpu().numpy().tobytes() == want.tobytes(), "n=%d chunk=%d rank %d" % (n, chunk, l)
-        assert lib.ga_set_option(ctx, 7, 0) == 0
+                assert view(l, n).cpu().numpy().tobytes() == want.tobytes(), "n=%d chunk=%d one=%d rank %d" % (n, chunk, one, l)
+        assert lib.ga_set_option(ctx, 7, 0) == 0 and lib.ga_set_option(ctx, 8, -1) == 0
         # fp32 sum and int32 sum (toy/main.py:19-20) in place
         n = 70001
         host = [rng.standard_normal(n).astype(np.float32) for _ in range(world)]
@@ -126,10 +129,11 @@ def test_adopted_gradients_train_like_the_drop_in_mode(built, world):
                 loss.backward()
                 if l == 0:
                     losses.append(loss)
-            if step == 3:
+            if step in (3, 4):
                 host = [[p.grad.cpu().numpy().copy() for p in n.parameters()] for n in nets]
-            avg.average_gradients_local(nets)
-            if step == 3:
+            # view mode: the in-place kernel on even steps, AUTO (bucket kernels on the region below 32 MiB) on odd ones
+            avg.average_gradients_local(nets, variant="view" if (mode == "view" and step % 2 == 0) else None)
+            if step in (3, 4):
                 for i in range(len(host[0])):
                     want = _fold([host[r][i].ravel() for r in range(world)])
                     for r in range(world):

@@ -207,6 +207,66 @@ __global__ void pingpong_kernel(volatile uint32_t *mine, volatile uint32_t *thei
     *out_ns = t1 - t0;
 }
 
+
+// Do system-scope fences issued by ONE thread slow down the other warps' remote stores?  Warps 1..15
+// stream the all-to-all copy; warp 0 lane 0 issues fence.acq_rel.sys back to back (mode 1), once per
+// `period` microseconds (mode 2), or never (mode 0), until the data warps are done.
+__global__ void __launch_bounds__(512, 2) fence_stream_kernel(Ptrs in, Ptrs out, int me, int G, size_t bytes_per_peer, int mode, int period_us,
+                                                              unsigned long long *stats) {
+    __shared__ unsigned int s_done;
+    if (threadIdx.x == 0) s_done = 0;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 0) {
+        if (lane == 0) {
+            unsigned long long n = 0, t_in = 0;
+            while (*(volatile unsigned int *)&s_done < 15u) {
+                if (mode == 0) continue;
+                unsigned long long a, b;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(a));
+                asm volatile("fence.acq_rel.sys;" ::: "memory");
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(b));
+                ++n; t_in += b - a;
+                if (mode == 2) { unsigned long long c = b; while (c - b < (unsigned long long)period_us * 1000ull && *(volatile unsigned int *)&s_done < 15u) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(c)); }
+            }
+            if (stats) { atomicAdd(stats, n); atomicAdd(stats + 1, t_in); }
+        }
+        return;
+    }
+    const size_t nvec = bytes_per_peer / 16;
+    const size_t tid = (size_t)blockIdx.x * 480 + (threadIdx.x - 32), nthr = (size_t)gridDim.x * 480;
+#pragma unroll 1
+    for (int jj = 1; jj < G; ++jj) {
+        const int peer = (me + jj) % G;
+        const uint4 *src = (const uint4 *)(in.p[me] + (size_t)peer * bytes_per_peer);
+        uint4 *dst = (uint4 *)(out.p[peer] + (size_t)me * bytes_per_peer);
+        size_t i = tid;
+        for (; i + 3 * nthr < nvec; i += 4 * nthr) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = __ldcg(src + i + u * nthr);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) __stcg(dst + i + u * nthr, v[u]);
+        }
+        for (; i < nvec; i += nthr) __stcg(dst + i, __ldcg(src + i));
+    }
+    __syncwarp();
+    if (lane == 0) atomicAdd(&s_done, 1u);
+}
+
+// cost of polling W flags one after the other (what a block barrier's poller does): W dependent
+// ld.relaxed.sys of local memory + one fence.acq_rel.sys, nothing outstanding
+__global__ void poll_cost_kernel(const uint32_t *flags, int W, unsigned long long *out_ns) {
+    unsigned long long t0, t1, t2;
+    uint32_t acc = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int s = 0; s < W; ++s) { uint32_t v; asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + s * 32) : "memory"); acc += v; }
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t2));
+    out_ns[0] = t1 - t0; out_ns[1] = t2 - t1; out_ns[2] = acc;
+}
+
 int G = 0;
 size_t bytes = 0;
 char *bufA[kMaxG], *bufB[kMaxG];
@@ -281,6 +341,22 @@ int main(int argc, char **argv) {
         timed("ld16", cfg, dir_bytes, [&](int d) { simt_kernel<16, true><<<g[0], g[1], 0, st[d]>>>(A, B, d, G, per_peer); });
         timed("ld32", cfg, dir_bytes, [&](int d) { simt_kernel<32, true><<<g[0], g[1], 0, st[d]>>>(A, B, d, G, per_peer); });
         timed("duplex16", cfg, dir_bytes, [&](int d) { duplex_kernel<<<g[0], g[1], 0, st[d]>>>(A, B, d, G, per_peer / 2 / 16 * 16); CK(cudaGetLastError()); });
+    }
+    {
+        unsigned long long *stats[kMaxG];
+        for (int d = 0; d < G; ++d) { CK(cudaSetDevice(d)); CK(cudaMalloc(&stats[d], 16)); }
+        const int modes[][2] = {{0, 0}, {1, 0}, {2, 20}, {2, 5}};
+        for (auto &m : modes) {
+            char cfg[96];
+            snprintf(cfg, sizeof cfg, "296 x 512 (15 data warps), fences: %s", m[0] == 0 ? "none" : m[0] == 1 ? "back to back by 1 thread per block" : m[1] == 20 ? "every 20 us" : "every 5 us");
+            for (int d = 0; d < G; ++d) { CK(cudaSetDevice(d)); CK(cudaMemset(stats[d], 0, 16)); }
+            timed("st16_fence", cfg, dir_bytes, [&](int d) { fence_stream_kernel<<<296, 512, 0, st[d]>>>(A, B, d, G, per_peer, m[0], m[1], stats[d]); CK(cudaGetLastError()); });
+            unsigned long long h[2]; CK(cudaSetDevice(0)); CK(cudaMemcpy(h, stats[0], 16, cudaMemcpyDeviceToHost));
+            printf("{\"fences_issued_gpu0_over_5_reps\": %llu, \"mean_fence_us\": %.2f}\n", h[0], h[0] ? (double)h[1] / h[0] / 1e3 : 0.0);
+        }
+        uint32_t *fl; unsigned long long *pc; CK(cudaSetDevice(0)); CK(cudaMalloc(&fl, 4096)); CK(cudaMemset(fl, 0, 4096)); CK(cudaMallocHost(&pc, 32));
+        for (int rep = 0; rep < 3; ++rep) { poll_cost_kernel<<<1, 1, 0, st[0]>>>(fl, 8, pc); CK(cudaStreamSynchronize(st[0])); }
+        printf("{\"poll_8_flags_sequentially_us\": %.2f, \"idle_fence_us\": %.2f}\n", pc[0] / 1e3, pc[1] / 1e3);
     }
     // note: duplex moves per_peer/2 bytes per peer pair as load data AND the same as store data, i.e. per_peer per pair per direction
     const int tma_cfg[][3] = {{148, 16384, 4}, {148, 32768, 4}, {148, 8192, 8}, {296, 16384, 4}, {74, 32768, 6}, {32, 32768, 6}};
