@@ -34,6 +34,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+_JSON_OUT = sys.stdout
 METRIC = "grad-avg bus GB/s"
 UNIT = "GB/s"
 DEFAULT_BYTES = 64 << 20
@@ -135,6 +136,22 @@ def cpu_reference(world, nbytes, steps, warmup, budget_s):
     }
 
 
+def cpu_train_reference(world, steps=40):
+    """BASELINE configs[1]: mnist/main.py:84-99 on gloo, `world` CPU processes on the box's host cores,
+    synthetic 128 x 1 x 28 x 28 batches; also the same step at world_size 1 (no averaging, :193)."""
+    from oracle import gloo_path
+    cores = os.cpu_count() or 1
+    threads = max(1, cores // world)
+    t0 = time.time()
+    out = {"world_size": world, "cores": min(cores, world * threads), "threads_per_rank": threads, "steps": steps, "batch_per_rank": 128,
+           "steps_per_sec": gloo_path.time_train_loop(world, steps=steps, warmup=4, batch=128, threads=threads),
+           "steps_per_sec_world1_no_averaging": gloo_path.time_train_loop(1, steps=steps, warmup=4, batch=128, threads=threads),
+           "what": "oracle/gloo_path.py:_train_job = mnist/main.py:84-99 restated (RefNet = :130-147), gloo tcp://127.0.0.1, "
+                   "host has %d cores%s" % (cores, ", oversubscribed" if world > cores else "")}
+    out["wall_s"] = time.time() - t0
+    return out
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -146,24 +163,29 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(world, args.gpus, args.bytes, "gloo ring (torch)", None),
+        "config": workload_config(world, args.gpus, args.bytes), "variant": "gloo ring (torch)", "l2": None,
         "cpu_baseline": cb,
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0, "wall_s": time.time() - t0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
 
 
-def workload_config(world, gpus, nbytes, variant, rotate):
+def workload_config(world, gpus, nbytes):
+    """The same dict in both arms (the driver compares it): arm-specific facts -- which kernel ran,
+    how L2 was defeated -- are top-level keys of the line, not part of the workload."""
     return {
         "workload": "gradient averaging of one %d-byte fp32 gradient per rank, world_size=%d (%s); "
                     "BASELINE configs[1] world size on 1 GPU, configs[3] 64 MiB bucket point"
                     % (nbytes, world, "%d ranks hosted per GPU" % (world // gpus) if gpus == 1 else "one rank per GPU"),
         "bytes_per_rank": nbytes, "world_size": world, "ranks_per_gpu": world // gpus if gpus == 1 else 1,
-        "variant": variant, "value_formula": "world * (S/t) * 2(world-1)/world",
-        "l2": None if rotate is None else "gradient buffers rotate over %d sets (%d MiB > L2) between steps"
-              % (rotate[0], rotate[1] >> 20),
+        "value_formula": "world * (S/t) * 2(world-1)/world",
+        "timed_call": "Trainer.average_gradients (mnist/main.py:122-127) on one gradient tensor per rank",
     }
+
+
+def l2_note(n_sets, total_bytes):
+    return "gradient buffers rotate over %d sets (%d MiB > L2) between steps" % (n_sets, total_bytes >> 20)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -184,6 +206,198 @@ def algorithmic_hbm_bytes(world, nbytes, variant_name, hosted):
     return per_rank * hosted
 
 
+NVLINK_NOMINAL = 900.0
+# profiles/r02_nvlink_probe.md: what this pool's fabric carries, per GPU and direction, both directions busy
+NVLINK_MEASURED = {"sm_stores_all_to_all_8gpu_gbps": 649.0, "sm_stores_2gpu_gbps": 665.0, "copy_engine_2gpu_gbps": 709.0,
+                   "copy_engine_all_to_all_8gpu_gbps": 404.0, "multimem_st_ingress_8gpu_gbps": 697.0,
+                   "guide_peer_copy_gbps": 770.0, "source": "tools/nvlink_probe.cu (profiles/r02_nvlink_probe.md); B200_PROFILING.md for the guide figure"}
+
+
+class _P:
+    """What `Trainer.average_gradients` iterates over: an object with `.grad` (mnist/main.py:125-127)."""
+    __slots__ = ("grad",)
+
+    def __init__(self, g):
+        self.grad = g
+
+
+def nvlink_counters(index):
+    """(tx_bytes, rx_bytes) summed over the GPU's links from `nvidia-smi nvlink -gt d`, or None."""
+    import re
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(index)], capture_output=True, text=True, timeout=20).stdout
+        tx = [int(x) for x in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out)]
+        rx = [int(x) for x in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out)]
+        if not tx or not rx:
+            return None
+        return sum(tx) * 1024, sum(rx) * 1024
+    except Exception:
+        return None
+
+
+def modes_leg(avg, vavg, world, hosted, S, sets, dev, multi, timed_loop, nvlink_roofline, hbm_peak):
+    """The same averaging through the library's other modes, 64 MiB per rank, each with its own roofline:
+      dropin_*   Trainer.average_gradients on ordinary gradient tensors (pack + exchange + unpack), other variants
+      view       gradients adopted into the peer-mapped region: in place, no pack / unpack; bit-exact
+      nvls       opt-in NVSwitch multimem: in-switch sum (correctly rounded, NOT rank order)"""
+    import torch
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import _lib
+    out, more = {}, []
+    n_sets = len(sets)
+    k, w = 60, 5
+    params = [[[_P(g)] for g in st] for st in sets]
+
+    def call(variant):
+        def f(i):
+            ps = params[i % n_sets]
+            if hosted == 1:
+                avg.average_gradients(ps[0], variant=variant)
+            else:
+                avg.average_gradients_local(ps, variant=variant)
+        return f
+
+    if multi:
+        for v in ("twoshot_pipe", "twoshot_push", "twoshot"):
+            ms, _ = timed_loop(call(v), k, w)
+            out["dropin_" + v] = {"ms_per_step": ms, "bus_gbps_per_rank": S / (ms / 1e3) * bus_factor(world) / 1e9, "bit_exact": True}
+    else:
+        for v in ("twoshot", "oneshot", "twoshot_pipe"):
+            ms, _ = timed_loop(call(v), k, w)
+            alg = algorithmic_hbm_bytes(world, S, v, hosted)
+            out["protocol_" + v] = {"ms_per_step": ms, "hbm_gbps": alg / (ms / 1e3) / 1e9, "bit_exact": True}
+            more.append({"bound": "hbm", "achieved": alg / (ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": alg / (ms / 1e3) / 1e9 / hbm_peak, "traffic": None,
+                         "kernel": {"twoshot": "ga_fused_kernel<%d,2,f32avg>", "oneshot": "ga_fused_kernel<%d,1,f32avg>",
+                                    "twoshot_pipe": "ga_push_pipe_kernel<%d,f32avg>"}[v] % world,
+                         "kernel_ms": ms, "what": "the cross-GPU protocol kernel (pack -> exchange -> unpack, flags) run by the "
+                                                  "hosted world on this one GPU: the code path N > 1 ships",
+                         "algorithmic": "%d hosted ranks x %.2f x S bytes per launch" % (hosted, alg / hosted / S)})
+    # view mode: every hosted rank's gradient lives in its view region
+    views = [vavg.view_tensor(S, l) for l in range(hosted)]
+    for v_, g in zip(views, sets[0]):
+        v_.copy_(g)
+    ms, _ = timed_loop(lambda i: vavg.allreduce_view(S, variant="view"), k, w)
+    out["view"] = {"ms_per_step": ms, "bit_exact": True, "grid": vavg.last_grid[0],
+                   "what": "GradAverager.adopt(): p.grad are views of the peer-mapped region, ga_average_view in place"}
+    if multi:
+        out["view"]["bus_gbps_per_rank"] = S / (ms / 1e3) * bus_factor(world) / 1e9
+        more.append(nvlink_roofline(ms, "ga_view_kernel<%d,f32avg>" % world, None))
+    else:
+        alg = hosted * (2.0 + 2.0 * (world - 1) / world + 2.0) * S   # scatter read+write (W-1)/W each, fold read S + write S
+        out["view"]["hbm_gbps"] = alg / (ms / 1e3) / 1e9
+        more.append({"bound": "hbm", "achieved": alg / (ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / hbm_peak,
+                     "traffic": None, "kernel": "ga_view_kernel<%d,f32avg>" % world, "kernel_ms": ms,
+                     "algorithmic": "%d hosted ranks x (2(W-1)/W scatter + 2 fold) x S bytes" % hosted})
+    if multi and vavg.has_multicast:
+        ms, _ = timed_loop(lambda i: vavg.allreduce_view(S, variant="nvls"), k, w)
+        r = nvlink_roofline(ms, "ga_nvls_kernel<f32avg>", None)
+        r["algorithmic"] += "; the in-switch form moves (N+1)/N * S per direction, the bus formula is kept for comparison with nccl-tests"
+        more.append(r)
+        out["nvls"] = {"ms_per_step": ms, "bus_gbps_per_rank": S / (ms / 1e3) * bus_factor(world) / 1e9, "bit_exact": False,
+                       "what": "opt-in GA_VARIANT_NVLS: multimem.ld_reduce + multimem.st; correctly rounded exact sum, not the rank-order fold"}
+    avg.check_status()
+    vavg.check_status()
+    return out, more
+
+
+def parity_leg(avg, vavg, world, rank, S, headline_grad, dev, dist):
+    """N > 1, outside the timed region: every variant AUTO can pick (and the view / NVLS modes) on the
+    seeded MNIST-CNN gradient set against the committed sha256 of the rank-order fold
+    (tests/golden/mnist_cnn.json: written by tests/golden/make_golden.py next to the REAL reference's
+    output), and one 64 MiB step against a sequential fp32 fold of the all-gathered inputs computed with
+    torch on the GPU.  Digests are all-gathered: every rank is checked, and must hold the same bytes."""
+    import hashlib
+    import numpy as np
+    import torch
+    from pytorch_distributed_example_b200 import workloads
+    out = {"world": world}
+    shapes = workloads.MNIST_CNN_SHAPES
+    g = torch.Generator().manual_seed(1234 + rank)                 # the seeding of oracle/gradient_sets.py and the golden files
+    host = [torch.randn(s, generator=g, dtype=torch.float32) for s in shapes]
+    golden = None
+    try:
+        golden = json.load(open(os.path.join(ROOT, "tests", "golden", "mnist_cnn.json")))["worlds"][str(world)]["signed"]["fold_sha256"]
+    except Exception:
+        pass
+
+    def digest(tensors):
+        flat = np.concatenate([t.detach().cpu().numpy().ravel() for t in tensors])
+        return hashlib.sha256(flat.tobytes()).digest()
+
+    def gather_digests(d):
+        t = torch.tensor(list(d), dtype=torch.uint8, device=dev)
+        outl = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outl, t)
+        return [bytes(o.cpu().tolist()) for o in outl]
+
+    def torch_fold(x, wide=False):
+        """((g0 + g1) + g2) + ... then one IEEE division, on the GPU; wide=True: binary64 sum rounded once (NVLS oracle)."""
+        gathered = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(gathered, x)
+        acc = gathered[0].double() if wide else gathered[0].clone()
+        for t in gathered[1:]:
+            acc = acc + (t.double() if wide else t)
+        acc = acc.float() if wide else acc
+        scale = torch.stack([t.abs() for t in gathered]).mean(0)
+        return acc / torch.full((), float(world), device=dev), scale
+
+    ok_all, identical = True, True
+    per_variant = {}
+    flat_in = torch.cat([t.ravel() for t in host]).to(dev)
+    want_fold, _ = torch_fold(flat_in)
+    for variant in ("auto", "oneshot_push", "twoshot_push", "twoshot_pipe", "oneshot", "twoshot"):
+        params = [_P(t.to(dev)) for t in host]
+        avg.average_gradients(params, variant=variant)
+        avg.check_status()
+        ds = gather_digests(digest([p.grad for p in params]))
+        same = all(d == ds[0] for d in ds)
+        good = (ds[0].hex() == golden) if golden else bool(torch.equal(torch.cat([p.grad.ravel() for p in params]).view(torch.int32), want_fold.view(torch.int32)))
+        per_variant[variant] = bool(good and same)
+        ok_all &= good
+        identical &= same
+    # view mode on the same set (flat layout), then NVLS against its own oracle
+    nb = flat_in.numel() * 4
+    v = vavg.view_tensor(nb)
+    v.copy_(flat_in)
+    vavg.allreduce_view(nb, variant="view")
+    vavg.check_status()
+    ds = gather_digests(digest([v]))
+    per_variant["view"] = bool(all(d == ds[0] for d in ds) and ((ds[0].hex() == golden) if golden else torch.equal(v.view(torch.int32), want_fold.view(torch.int32))))
+    ok_all &= per_variant["view"]
+    out["mnist_sha_ok"] = bool(ok_all)
+    out["mnist_per_variant"] = per_variant
+    out["golden"] = "tests/golden/mnist_cnn.json fold_sha256" if golden else "torch rank-order fold on the GPU (world size not in the golden file)"
+    # headline buffer: one step, AUTO and view, bit for bit against the sequential fold
+    x = headline_grad.clone()
+    want, scale = torch_fold(x)
+    p = [_P(x.clone())]
+    avg.average_gradients(p)
+    exact_auto = bool(torch.equal(p[0].grad.view(torch.int32), want.view(torch.int32)))
+    hv = vavg.view_tensor(S)
+    hv.copy_(x)
+    vavg.allreduce_view(S, variant="view")
+    exact_view = bool(torch.equal(hv.view(torch.int32), want.view(torch.int32)))
+    ds = gather_digests(hashlib.sha256(hv.cpu().numpy().tobytes()).digest())
+    identical &= all(d == ds[0] for d in ds)
+    out["headline_bit_exact"] = bool(exact_auto and exact_view)
+    out["headline_bit_exact_by_mode"] = {"auto": exact_auto, "view": exact_view}
+    out["ranks_identical"] = bool(identical)
+    if vavg.has_multicast:
+        wide, _ = torch_fold(x, wide=True)
+        hv.copy_(x)
+        vavg.allreduce_view(S, variant="nvls")
+        vavg.check_status()
+        eq = float((hv.view(torch.int32) == wide.view(torch.int32)).float().mean())
+        err = float(((hv - want).abs() / scale.clamp_min(1e-30)).max())
+        ds = gather_digests(hashlib.sha256(hv.cpu().numpy().tobytes()).digest())
+        out["nvls"] = {"equal_to_wide_sum_oracle": eq, "max_abs_err_vs_rank_order_over_mean_abs_input": err,
+                       "ranks_identical": all(d == ds[0] for d in ds), "gate": "err <= 1e-6 (north_star's fp32 tolerance, SURVEY F3 metric); opt-in, not bit-exact"}
+        out["nvls_ok"] = bool(err <= 1e-6 and out["nvls"]["ranks_identical"])
+    out["ok"] = bool(out["mnist_sha_ok"] and out["headline_bit_exact"] and out["ranks_identical"] and out.get("nvls_ok", True))
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -200,6 +414,10 @@ def main():
     ap.add_argument("--profile", action="store_true", help="bare loop for ncu: no extras, no cpu leg, no e2e")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    # stdout carries the ONE JSON line: whatever libraries print (NCCL's version banner, warnings) is sent to stderr
+    global _JSON_OUT
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference_arm(args)
         return
@@ -239,12 +457,18 @@ def main():
     variant_name = names[variant_id]
 
     # gradient sets: rotate so that consecutive steps never find their inputs in L2
-    n_sets = max(2, min(64, -(-(300 << 20) // (hosted * S))))
+    n_sets = max(2, min(16, -(-(300 << 20) // (hosted * S))))
     gen = torch.Generator(device=dev).manual_seed(1234 + rank)
     sets = [[torch.randn(n, device=dev, generator=gen) for _ in range(hosted)] for _ in range(n_sets)]
+    # what Trainer.average_gradients receives: parameters whose .grad is the gradient (mnist/main.py:125-127)
+    param_sets = [[[_P(g)] for g in st] for st in sets]
 
     def step(i):
-        avg.all_reduce_([[g] for g in sets[i % n_sets]], average=True, variant=variant_id)
+        ps = param_sets[i % n_sets]
+        if hosted == 1:
+            avg.average_gradients(ps[0], variant=variant_id)          # GradAverager._run_params -> ga_average
+        else:
+            avg.average_gradients_local(ps, variant=variant_id)
 
     def barrier():
         if multi:
@@ -258,32 +482,38 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
+    def timed_loop(fn, steps, warmup):
+        """K calls between two CUDA events on the launching stream, barrier + synchronize on both sides,
+        max over ranks; returns (ms per call, wall-clock window)."""
+        for i in range(warmup):
+            fn(i)
+        avg.check_status()                  # a peer that never arrives surfaces here, not as a hung bench
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
+        e0.record()
+        for i in range(steps):
+            fn(i)
+        e1.record()
+        torch.cuda.synchronize()
+        if multi:
+            dist.barrier()
+        w1 = time.time()
+        avg.check_status()
+        return max_over_ranks(e0.elapsed_time(e1)) / steps, (w0, w1)
+
     sampler = ClockSampler(index=torch.cuda.current_device()) if rank == 0 else None
     windows = []
 
-    # ---- value: device-resident, K steps between two events, plus one event pair per launch ------
+    # ---- value: device-resident, K steps between two events ---------------------------------------
     stage("context ready: world=%d hosted=%d S=%d variant=%s sets=%d" % (world, hosted, S, variant_name, n_sets))
-    for i in range(args.warmup):
-        step(i)
-    avg.check_status()                      # a peer that never arrives surfaces here, not as a hung bench
-    barrier()
-    stage("warm-up done, grid=%s" % (avg.last_grid,))
     launches0 = avg.launch_count
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
-    w0 = time.time()
-    ev[0].record()
-    for i in range(args.steps):
-        step(i)
-    ev[1].record()
-    torch.cuda.synchronize()
-    if multi:
-        dist.barrier()
-    windows.append((w0, time.time()))
-    gpu_launches = avg.launch_count - launches0
-    avg.check_status()
-    stage("timed region done")
-    total_ms = max_over_ranks(ev[0].elapsed_time(ev[1]))
-    ms_per_step = total_ms / args.steps
+    nv0 = nvlink_counters(torch.cuda.current_device()) if multi and rank == 0 else None
+    ms_per_step, win = timed_loop(step, args.steps, args.warmup)
+    nv1 = nvlink_counters(torch.cuda.current_device()) if multi and rank == 0 else None
+    windows.append(win)
+    gpu_launches = avg.launch_count - launches0 - args.warmup
+    stage("timed region done: %.1f us per step, grid=%s" % (ms_per_step * 1e3, avg.last_grid))
     kernel_ms = ms_per_step          # one launch per step: average launch duration incl. the launch gap
     value = agg_bus_gbps(world, S, ms_per_step / 1e3)
     grid = avg.last_grid
@@ -291,18 +521,33 @@ def main():
     # ---- roofline of the one kernel -------------------------------------------------------------
     hbm_peak, peak_src = load_peaks()
     alg_bytes = algorithmic_hbm_bytes(world, S, variant_name, hosted)
+    kernel_names = {"oneshot": "ga_fused_kernel<%d,1,f32avg>", "twoshot": "ga_fused_kernel<%d,2,f32avg>",
+                    "oneshot_push": "ga_push1_kernel<%d,f32avg>", "twoshot_push": "ga_push_kernel<%d,f32avg>",
+                    "twoshot_pipe": "ga_push_pipe_kernel<%d,f32avg>", "hosted_direct": "ga_hosted_direct_kernel<%d,f32avg>",
+                    "view": "ga_view_kernel<%d,f32avg>"}
+
+    def nvlink_roofline(ms, kernel, traffic):
+        bus = (S / (ms / 1e3)) * bus_factor(world) / 1e9
+        return {"bound": "nvlink", "achieved": bus, "peak": NVLINK_NOMINAL, "unit": "GB/s", "frac": bus / NVLINK_NOMINAL,
+                "traffic": traffic, "kernel": kernel, "kernel_ms": ms,
+                "peak_source": "nominal NVLink 5 per direction per GPU (north_star)",
+                "peak_measured": NVLINK_MEASURED, "frac_of_measured": bus / NVLINK_MEASURED["sm_stores_all_to_all_8gpu_gbps"],
+                "algorithmic": "busBW = S/t * 2(N-1)/N per GPU; link bytes per GPU and direction 2(N-1)/N * S = %d"
+                               % int(S * bus_factor(world))}
+
     if multi:
-        bus = (S / (kernel_ms / 1e3)) * bus_factor(world) / 1e9
-        roofline = {"bound": "nvlink", "achieved": bus, "peak": 900.0, "unit": "GB/s", "frac": bus / 900.0,
-                    "traffic": None, "kernel": "ga_fused_kernel<%d,%s,f32avg>" % (world, variant_name),
-                    "kernel_ms": kernel_ms, "peak_source": "nominal NVLink 5 per direction per GPU (north_star); "
-                    "measured peer copy on this pool is 770 GB/s (B200_PROFILING.md)",
-                    "algorithmic": "busBW = S/t * 2(N-1)/N per GPU",
-                    "hbm_side": {"bytes": alg_bytes, "gbps": alg_bytes / (kernel_ms / 1e3) / 1e9, "peak": hbm_peak}}
+        traffic = None
+        if nv0 and nv1:
+            k = args.steps + args.warmup
+            traffic = {"tx_bytes_per_launch": (nv1[0] - nv0[0]) / k, "rx_bytes_per_launch": (nv1[1] - nv0[1]) / k,
+                       "source": "nvidia-smi nvlink -gt d on rank 0's GPU before / after the warm-up + timed launches",
+                       "algorithmic_per_direction": S * bus_factor(world)}
+        roofline = nvlink_roofline(kernel_ms, kernel_names[variant_name] % world, traffic)
+        roofline["hbm_side"] = {"bytes": alg_bytes, "gbps": alg_bytes / (kernel_ms / 1e3) / 1e9, "peak": hbm_peak}
     else:
         ach = alg_bytes / (kernel_ms / 1e3) / 1e9
         roofline = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                    "traffic": load_traffic(), "kernel": "ga_fused_kernel<%d,%s,f32avg>" % (world, variant_name),
+                    "traffic": load_traffic(), "kernel": kernel_names[variant_name] % world,
                     "kernel_ms": kernel_ms, "peak_source": peak_src,
                     "algorithmic": "%d hosted ranks x %.2f x S bytes per launch (DESIGN.md kernel table)"
                                    % (hosted, alg_bytes / hosted / S)}
@@ -311,10 +556,27 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(world, args.gpus, S, variant_name, (n_sets, n_sets * hosted * S)),
+        "config": workload_config(world, args.gpus, S), "variant": variant_name, "l2": l2_note(n_sets, n_sets * hosted * S),
         "bus_gbps_per_rank": value / world, "alg_gbps_per_rank": S / (ms_per_step / 1e3) / 1e9,
         "roofline": roofline, "gpu_launches": gpu_launches, "grid": {"blocks_per_rank": grid[0], "threads": grid[1]},
     }
+
+    if not args.profile:
+        # ---- the other ways to make the same call (same gradients, same result bits unless said otherwise) ----
+        stage("modes leg")
+        # the view region pins its context's size, so the in-place modes get a context of their own
+        vavg = ga.GradAverager(capacity_bytes=S) if multi else ga.GradAverager(local_world=world, device=0, capacity_bytes=S)
+        vavg.create_view(S, multicast=True)
+        line["modes"], more = modes_leg(avg, vavg, world, hosted, S, sets, dev, multi, timed_loop, nvlink_roofline, hbm_peak)
+        line["roofline_more"] = more
+        if multi:
+            stage("parity leg")
+            line["parity"] = parity_leg(avg, vavg, world, rank, S, sets[0][0], dev, dist)
+        gpu_launches_other = vavg.launch_count
+        if multi:
+            dist.barrier()
+        vavg.close()
+        line["gpu_launches_outside_timed_region"] = gpu_launches_other
 
     if not args.profile:
         # ---- e2e: host buffers through ga_average_host ------------------------------------------
@@ -343,25 +605,19 @@ def main():
                        "steps": e2e_steps, "h2d_bytes_per_step": hosted * S, "d2h_bytes_per_step": hosted * S,
                        "api": "GradAverager.average_host -> ga_average_host (pinned host fp32 tensors)"}
 
-        # ---- NCCL on a same-size buffer, same run (N > 1) ---------------------------------------
+        # ---- NCCL on a same-size buffer, same run (N > 1): all_reduce alone, and with the reference's div_ ----
         if multi:
             buf = torch.randn(n, device=dev, generator=gen)
-            for _ in range(5):
-                dist.all_reduce(buf)
-                buf.div_(float(world))
-            barrier()
             k = max(10, min(args.steps, 100))
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            for _ in range(k):
-                dist.all_reduce(buf)               # mnist/main.py:126 on NCCL
-                buf.div_(float(world))             # mnist/main.py:127
-            e1.record()
-            torch.cuda.synchronize()
+            nccl_ms, _ = timed_loop(lambda i: dist.all_reduce(buf), k, 5)                          # mnist/main.py:126 on NCCL
+            nccl_div_ms, _ = timed_loop(lambda i: (dist.all_reduce(buf), buf.div_(float(world))), k, 5)   # + mnist/main.py:127
             stage("nccl comparison done")
-            nccl_ms = max_over_ranks(e0.elapsed_time(e1)) / k
-            line["nccl_same_buffer"] = {"ms_per_step": nccl_ms, "bus_gbps_per_rank": S / (nccl_ms / 1e3) * bus_factor(world) / 1e9,
-                                        "what": "torch.distributed.all_reduce(SUM) + div_ on one %d-byte buffer" % S}
+            line["nccl_same_buffer"] = {
+                "allreduce_only": {"ms_per_step": nccl_ms, "bus_gbps_per_rank": S / (nccl_ms / 1e3) * bus_factor(world) / 1e9},
+                "allreduce_plus_div": {"ms_per_step": nccl_div_ms, "bus_gbps_per_rank": S / (nccl_div_ms / 1e3) * bus_factor(world) / 1e9},
+                "ms_per_step": nccl_div_ms,
+                "what": "torch.distributed.all_reduce(SUM) on one %d-byte buffer (in place), alone and followed by div_ "
+                        "(what the reference's loop does per tensor); NCCL's sum order is its own (NVLS / ring), not rank order" % S}
 
         if not args.no_extras and rank == 0 and not multi:
             line["extras"] = extras_single_gpu(avg, world, dev)
@@ -372,7 +628,7 @@ def main():
             stage("overlap leg")
             line["resnet18_overlap"] = overlap_leg(avg, world, dev, dist)
         if multi and args.sweep:
-            line["sweep"] = sweep_multi(avg, world, dev, dist, args.sweep_max)
+            line["sweep"] = sweep_multi(avg, world, dev, dist, args.sweep_max, rank)
         if multi and args.explore:
             line["explore"] = explore_pipe(avg, world, dev, dist)
 
@@ -382,21 +638,30 @@ def main():
     if not args.profile and not args.no_extras and rank == 0 and not multi:
         # CPU leg last, GPU idle, N = 1 only: the reference's averaging on host cores, bounded sample
         line["cpu_baseline"] = cpu_reference(world, S, steps=12, warmup=2, budget_s=20.0)
+        # second half of the metric on the same host cores: the reference's training step on gloo (configs[1])
+        if isinstance(line.get("mnist_steps_per_sec"), dict):
+            line["mnist_steps_per_sec"]["cpu_reference_gloo"] = cpu_train_reference(world)
 
     if multi:
         dist.barrier()
     avg.close()
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     if multi:
         dist.destroy_process_group()
+    if line.get("parity") is not None and not line["parity"]["ok"]:
+        raise SystemExit("bench.py: PARITY FAILED at N=%d: %s" % (args.gpus, json.dumps(line["parity"])))
 
 
-def sweep_multi(avg, world, dev, dist, max_bytes):
-    """Config 4: flat fp32 buffer, 4 KB * 4^k up to 1 GB plus the two real set sizes; per size the
-    fused call (pack + reduce + unpack on a gradient tensor), the bucket-direct call (reduce only),
-    both variants, and NCCL all_reduce + div_ on the same-size buffer.  Median of per-iteration
-    max over ranks, device-timed."""
+def sweep_multi(avg, world, dev, dist, max_bytes, rank=0):
+    """Config 4: flat fp32 buffer, 4 KB * 4^k up to 1 GB plus the two real set sizes.  Per size:
+      fused_*    Trainer.average_gradients on a gradient tensor (pack + exchange + unpack), every variant and AUTO
+      bucket_*   the bucket-direct call (reduce only, input already in the bucket)
+      view*      in place on the peer-mapped view region (GA_VARIANT_VIEW; view_auto = what adopt() runs)
+      nvls       opt-in in-switch variant (not rank order)
+      nccl_*     torch.distributed.all_reduce alone, and + div_ (the reference's per-tensor pair), same size, in place
+      gloo       the reference's CPU path on the box's host cores (one gloo session over all sizes, rank 0's host)
+    Median of per-iteration max over ranks, device-timed."""
     import torch
     import pytorch_distributed_example_b200 as ga
     from pytorch_distributed_example_b200 import _lib
@@ -404,6 +669,8 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
              256 << 20, 1 << 30]
     sizes = [s for s in sizes if s <= max_bytes]
     avg.reserve(max(sizes) + 4096)
+    vavg = ga.GradAverager(capacity_bytes=max(sizes) + 4096)
+    vavg.create_view(max(sizes) + 4096, multicast=True)
     out = []
 
     def timed(fn, iters, warm=5):
@@ -421,6 +688,9 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         t = t.sort().values
         return float(t[iters // 2]) * 1e3, float(t[0]) * 1e3          # median, best (us)
+
+    def cell(med, best, S):
+        return {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
 
     # what the harness itself costs per iteration (Python call + event record, max over ranks): sizes
     # whose times sit near this floor are host-bound, not kernel-bound
@@ -444,8 +714,7 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
             def fused():
                 k[0] += 1
                 avg.all_reduce_([[bufs[k[0] % len(bufs)]]], average=True, variant=v)
-            med, best = timed(fused, iters)
-            row["fused_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+            row["fused_" + vname] = cell(*timed(fused, iters), S)
             if vname == "auto":
                 row["fused_auto"]["picked"] = avg.pick_variant(S)
             if vname.endswith("_push") or vname.endswith("_pipe") or vname == "auto":
@@ -454,24 +723,53 @@ def sweep_multi(avg, world, dev, dist, max_bytes):
 
             def bucket():
                 avg.allreduce_bucket(S, variant=v)
-            med, best = timed(bucket, iters)
-            row["bucket_" + vname] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+            row["bucket_" + vname] = cell(*timed(bucket, iters), S)
+        vt = vavg.view_tensor(S)
+        vt.copy_(bufs[0])
+        row["view"] = cell(*timed(lambda: vavg.allreduce_view(S, variant="view"), iters), S)
+        row["view_auto"] = cell(*timed(lambda: vavg.allreduce_view(S), iters), S)
+        if vavg.has_multicast:
+            row["nvls"] = cell(*timed(lambda: vavg.allreduce_view(S, variant="nvls"), iters), S)
 
         def nccl():
+            k[0] += 1
+            dist.all_reduce(bufs[k[0] % len(bufs)])
+
+        def nccl_div():
             k[0] += 1
             b = bufs[k[0] % len(bufs)]
             dist.all_reduce(b)
             b.div_(float(world))
-        med, best = timed(nccl, iters)
-        row["nccl_allreduce_div"] = {"us": med, "best_us": best, "bus_gbps": S / med / 1e3 * bus_factor(world)}
+        row["nccl_allreduce"] = cell(*timed(nccl, iters), S)
+        row["nccl_allreduce_div"] = cell(*timed(nccl_div, iters), S)
         if S <= (4 << 20):
             # host-free latency: 20 back-to-back calls captured in one CUDA graph, replayed
             row["graph_auto"] = graph_latency(lambda b: avg.all_reduce_([[b]], average=True), bufs, dev, dist)
+            row["graph_nccl_allreduce"] = graph_latency(lambda b: dist.all_reduce(b), bufs, dev, dist)
             row["graph_nccl_allreduce_div"] = graph_latency(lambda b: (dist.all_reduce(b), b.div_(float(world))), bufs, dev, dist)
         out.append(row)
         del bufs
         avg.check_status()
+        vavg.check_status()
         stage("sweep %d bytes: %s" % (S, {k2: round(v2["us"], 1) for k2, v2 in row.items() if isinstance(v2, dict)}))
+    dist.barrier()
+    vavg.close()
+    # the reference's CPU path on the host cores, every size, while the GPUs idle (rank 0's process only)
+    if rank == 0:
+        try:
+            from oracle import gloo_path
+            cores = os.cpu_count() or 1
+            threads = max(1, cores // world)
+            gl = [s for s in sizes if s <= (256 << 20) or world <= 4]
+            secs = gloo_path.time_flat_average_sizes(world, [s // 4 for s in gl], iters=5, warmup=1, threads=threads)
+            for row in out:
+                if row["bytes"] in gl:
+                    t = secs[gl.index(row["bytes"])]
+                    row["gloo_cpu"] = {"us": t * 1e6, "bus_gbps": row["bytes"] / t / 1e9 * bus_factor(world), "cores": min(cores, world * threads),
+                                       "what": "oracle/gloo_path.py (mnist/main.py:122-127 restated), %d procs x %d threads" % (world, threads)}
+        except Exception as e:                                  # report, never fake
+            out.append({"gloo_cpu_error": "%s: %s" % (type(e).__name__, str(e)[:300])})
+    dist.barrier()
     return out
 
 

@@ -141,3 +141,87 @@ def _set_job(rank, world, shapes, iters, warmup, base_seed):
 
 def time_set_average(world, shapes, iters, warmup=1, threads=1, base_seed=1234):
     return run_world(world, _set_job, (shapes, iters, warmup, base_seed), threads=threads)[0]
+
+
+def _flat_multi_job(rank, world, numels, iters, warmup, base_seed):
+    out = []
+    for numel in numels:
+        g = torch.Generator().manual_seed(base_seed + rank)
+        buf = torch.randn(numel, generator=g, dtype=torch.float32)
+        p = [_P(buf)]
+        times = []
+        n_it = iters if numel * 4 < (256 << 20) else max(2, iters // 3)
+        for i in range(warmup + n_it):
+            dist.barrier()
+            t0 = time.perf_counter()
+            average_gradients_ref(p, world)
+            t1 = time.perf_counter()
+            t = torch.tensor([t1 - t0], dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            if i >= warmup:
+                times.append(float(t))
+        out.append(sorted(times)[len(times) // 2])
+        del buf, p
+    return out
+
+
+def time_flat_average_sizes(world, numels, iters=5, warmup=1, threads=1, base_seed=1234):
+    """Median wall-clock seconds of the reference-style averaging for each flat buffer size, in ONE
+    gloo session (the size sweep of BASELINE.json configs[3])."""
+    return run_world(world, _flat_multi_job, (list(numels), iters, warmup, base_seed), threads=threads)[0]
+
+
+class RefNet(torch.nn.Module):
+    """The reference model restated (`/root/reference/mnist/main.py:130-147`): conv(1->20,5) -> pool ->
+    conv(20->50,5) -> pool -> fc(800->500) -> fc(500->10) -> log_softmax."""
+
+    def __init__(self):
+        super().__init__()
+        self.conv1 = torch.nn.Conv2d(1, 20, 5, 1)
+        self.conv2 = torch.nn.Conv2d(20, 50, 5, 1)
+        self.fc1 = torch.nn.Linear(4 * 4 * 50, 500)
+        self.fc2 = torch.nn.Linear(500, 10)
+
+    def forward(self, x):
+        F = torch.nn.functional
+        x = F.max_pool2d(F.relu(self.conv1(x)), 2, 2)
+        x = F.max_pool2d(F.relu(self.conv2(x)), 2, 2)
+        x = F.relu(self.fc1(x.view(-1, 4 * 4 * 50)))
+        return F.log_softmax(self.fc2(x), dim=1)
+
+
+def _train_job(rank, world, steps, warmup, batch):
+    """The reference step on the CPU (`mnist/main.py:84-99`): forward, cross_entropy, zero_grad, backward,
+    average_gradients (when world > 1, :94-95), Adam step, loss.item(); synthetic 28x28 batches."""
+    F = torch.nn.functional
+    torch.manual_seed(0)
+    net = RefNet()
+    opt = torch.optim.Adam(net.parameters(), lr=1e-3)         # :187, :229
+    g = torch.Generator().manual_seed(777 + rank)
+    data = torch.randn(batch, 1, 28, 28, generator=g)
+    label = torch.randint(0, 10, (batch,), generator=g)
+    t0 = None
+    for i in range(warmup + steps):
+        if i == warmup:
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+        output = net(data)                                    # :88
+        loss = F.cross_entropy(output, label)                 # :89
+        opt.zero_grad()                                       # :91
+        loss.backward()                                       # :92
+        if world > 1:
+            average_gradients_ref(net.parameters(), world)    # :94-95
+        opt.step()                                            # :96
+        loss.item()                                           # :98
+    dt = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([dt], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = float(t)
+    return steps / dt
+
+
+def time_train_loop(world, steps=60, warmup=5, batch=128, threads=1):
+    """Synchronous data-parallel steps per second of the reference training step on `world` gloo CPU ranks."""
+    return run_world(world, _train_job, (steps, warmup, batch), threads=threads)[0]
