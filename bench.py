@@ -601,9 +601,30 @@ def main():
         avg.check_status()
         stage("e2e done")
         e2e_ms = max_over_ranks(e0.elapsed_time(e1)) / e2e_steps
+        # the floor under it: the same bytes copied in and out at once (two streams), no kernel, every rank at the same time
+        scratch = [torch.empty(n, device=dev) for _ in range(hosted)]
+        s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+        def bare(i):
+            cur = torch.cuda.current_stream()
+            s_in.wait_stream(cur)
+            s_out.wait_stream(cur)
+            with torch.cuda.stream(s_in):
+                for t, d_ in zip(host_sets[0], scratch):
+                    d_.copy_(t, non_blocking=True)
+            with torch.cuda.stream(s_out):
+                for t, g_ in zip(host_sets[1], sets[0]):
+                    t.copy_(g_, non_blocking=True)
+            cur.wait_stream(s_in)
+            cur.wait_stream(s_out)
+        bare_ms, _ = timed_loop(bare, 6, 2)
+        del scratch
         line["e2e"] = {"value": agg_bus_gbps(world, S, e2e_ms / 1e3), "unit": UNIT, "ms_per_step": e2e_ms,
                        "steps": e2e_steps, "h2d_bytes_per_step": hosted * S, "d2h_bytes_per_step": hosted * S,
-                       "api": "GradAverager.average_host -> ga_average_host (pinned host fp32 tensors)"}
+                       "api": "GradAverager.average_host -> ga_average_host (pinned host fp32 tensors)",
+                       "bare_copy_floor_ms": bare_ms,
+                       "floor_what": "H2D and D2H of the same bytes at once on two streams, no kernel, all %d rank(s) at the same "
+                                     "time (PCIe and host memory are shared by the GPUs of the box)" % world}
 
         # ---- NCCL on a same-size buffer, same run (N > 1): all_reduce alone, and with the reference's div_ ----
         if multi:
@@ -926,11 +947,13 @@ def mnist_leg(avg, world, hosted, dev, dist, rank, steps=200, batch=128):
     return out
 
 
-def overlap_leg(avg, world, dev, dist, steps=30, batch=32):
+def overlap_leg(avg, world, dev, dist, steps=20, batch=128):
     """BASELINE configs[4]: ResNet-18 (62 gradient tensors, 46.76 MB) forward + backward on
-    randn(32,3,224,224); per-step averaging (a) absent, (b) one fused call after backward (the
-    reference's call site), (c) bucketed and overlapped with backward from grad hooks.  Exposed
-    averaging time = step time minus (a).  Device-timed, max over ranks."""
+    randn(128,3,224,224) per rank (batch 128 so that backward, not the host, sets the step time);
+    per-step averaging (a) absent, (b) one fused call after backward (the reference's call site),
+    (c) bucketed and overlapped with backward from grad hooks, forced on, (d) the same object left to
+    decide for itself (it refuses when the exchange it could hide is shorter than what the hooks cost).
+    Exposed averaging time = step time minus (a).  Device-timed, max over ranks."""
     import torch
     import torch.nn.functional as F
     import pytorch_distributed_example_b200 as ga
@@ -957,7 +980,7 @@ def overlap_leg(avg, world, dev, dist, steps=30, batch=32):
             ov[0].average_gradients()
 
     def timed(mode):
-        for _ in range(5):
+        for _ in range(4):
             step(mode)
         torch.cuda.synchronize()
         dist.barrier()
@@ -971,16 +994,23 @@ def overlap_leg(avg, world, dev, dist, steps=30, batch=32):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
-    out = {"model": "torchvision resnet18, batch %d, fp32, channels_last" % batch,
+    out = {"model": "torchvision resnet18, batch %d per rank, fp32, channels_last" % batch,
            "grad_bytes": sum(p.numel() for p in params) * 4, "tensors": len(params)}
     out["ms_no_averaging"] = timed("none")
     out["ms_fused_after_backward"] = timed("after")
-    ov[0] = ga.OverlappedAverager(net, averager=avg, bucket_cap_bytes=16 << 20, max_blocks=32)
+    ov[0] = ga.OverlappedAverager(net, averager=avg, bucket_cap_bytes=16 << 20, max_blocks=32, force=True)
     out["buckets"] = len(ov[0].buckets)
+    out["ms_overlapped_forced"] = timed("overlap")
+    ov[0].remove()
+    ov[0] = ga.OverlappedAverager(net, averager=avg, bucket_cap_bytes=16 << 20, max_blocks=32)
+    out["self_gating"] = {"enabled": ov[0].enabled, "reason": ov[0].reason}
     out["ms_overlapped"] = timed("overlap")
     ov[0].remove()
-    out["exposed_us_after_backward"] = (out["ms_fused_after_backward"] - out["ms_no_averaging"]) * 1e3
-    out["exposed_us_overlapped"] = (out["ms_overlapped"] - out["ms_no_averaging"]) * 1e3
+    out["ms_no_averaging_again"] = timed("none")               # the step itself drifts: bracket it
+    base = 0.5 * (out["ms_no_averaging"] + out["ms_no_averaging_again"])
+    out["exposed_us_after_backward"] = (out["ms_fused_after_backward"] - base) * 1e3
+    out["exposed_us_overlapped_forced"] = (out["ms_overlapped_forced"] - base) * 1e3
+    out["exposed_us_overlapped"] = (out["ms_overlapped"] - base) * 1e3
     avg.check_status()
     return out
 

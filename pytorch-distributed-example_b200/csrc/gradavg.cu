@@ -934,16 +934,40 @@ namespace {
 
 size_t tiles_for_elems(int64_t numel) { return (size_t)((numel + kTileElems - 1) / kTileElems); }
 
-// AUTO thresholds, from the round-1 sweeps (profiles/): hosted worlds move everything through HBM
-// and prefer the pull kernels; across GPUs the push kernels win at every size, one-shot while its
-// (world-1)*S egress stays below ~8 MiB.
+// AUTO, one rank per GPU: which kernel is quickest for a set of `bytes`, per world-size class, read
+// off the committed sweeps of this pool (profiles/r02_bench_n{2,4,8}_sweep.json; tests/test_abi.py
+// re-checks every row of those files: AUTO's pick must be within 3 % of the best fused variant).
+//   world 2      one-shot push up to 32 MiB (same link bytes as two-shot, one barrier less), two-shot push beyond
+//   world 3..8   one-shot push while its (world-1)*S egress stays below 8 MiB, then the pipelined kernel in
+//                its one-round form up to 32 MiB, two-shot push beyond (its rounds no longer pay: the round-1
+//                gain of 3-10 % between 32 and 128 MiB is gone since the barriers poll with one thread)
+struct AutoRow { int world_max; size_t bytes_max_num, bytes_max_div_world_minus_1; int variant; };
+constexpr AutoRow kAutoTable[] = {
+    {2, (size_t)32 << 20, 0, GA_VARIANT_ONESHOT_PUSH},
+    {2, (size_t)-1, 0, GA_VARIANT_TWOSHOT_PUSH},
+    {8, (size_t)8 << 20, 1, GA_VARIANT_ONESHOT_PUSH},
+    {8, (size_t)32 << 20, 0, GA_VARIANT_TWOSHOT_PIPE},
+    {8, (size_t)-1, 0, GA_VARIANT_TWOSHOT_PUSH},
+};
+
+int auto_from_table(int world, size_t bytes) {
+    for (const AutoRow &r : kAutoTable) {
+        if (world > r.world_max) continue;
+        const size_t lim = r.bytes_max_div_world_minus_1 ? r.bytes_max_num / (size_t)(world > 1 ? world - 1 : 1) : r.bytes_max_num;
+        if (bytes <= lim) return r.variant;
+    }
+    return GA_VARIANT_TWOSHOT_PUSH;
+}
+
+// Thresholds of the remaining cases (hosted sub-worlds move everything through HBM and prefer the
+// pull kernels) and of GA_OPT_ONESHOT_MAX_BYTES, which overrides the table's first row when set.
 void set_auto_thresholds(ga_ctx *c) {
     const int world = c->world, n_local = c->n_local;
-    if (world <= 2) c->oneshot_max_bytes = (size_t)32 << 20;   // same link bytes either way; two-shot stages less (r01m sweep)
+    if (world <= 2) c->oneshot_max_bytes = (size_t)32 << 20;
     else if (n_local > 1) c->oneshot_max_bytes = (size_t)512 << 10;
     else c->oneshot_max_bytes = ((size_t)8 << 20) / (size_t)(world - 1);
     c->pipe_min_bytes = (size_t)32 << 20;
-    c->pipe_max_bytes = (size_t)128 << 20;
+    c->pipe_max_bytes = (size_t)32 << 20;
 }
 
 int create_body(ga_ctx *c, int device);
@@ -970,7 +994,8 @@ int create_common(int rank_base, int n_local, int world, int device, size_t capa
     c->timeout_ns = 30ull * 1000000000ull;
     c->host_chunk_bytes = (size_t)8 << 20;
     c->view_oneshot_max_opt = -1;
-    c->view_min_bytes = (size_t)32 << 20;
+    // world 2: two-shot push on the region is as quick as the in-place kernel at every size (r02 N=2 sweep)
+    c->view_min_bytes = world <= 2 ? (size_t)-1 : (size_t)32 << 20;
     const char *env = getenv("GA_TIMEOUT_MS");
     if (env) c->timeout_ns = strtoull(env, nullptr, 10) * 1000000ull;
     const int rc = create_body(c, device);
@@ -1499,8 +1524,15 @@ int ga_pick_variant(const ga_ctx *c, size_t nbytes) {
     const bool one_shot = nbytes <= c->oneshot_max_bytes;
     if (c->n_local > 1 && c->n_local == c->world) return GA_VARIANT_HOSTED_DIRECT;
     if (c->n_local > 1 || c->world == 1) return one_shot ? GA_VARIANT_ONESHOT : GA_VARIANT_TWOSHOT;
-    if (one_shot && nbytes * c->world <= c->capacity_bytes) return GA_VARIANT_ONESHOT_PUSH;
-    return nbytes <= c->pipe_max_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH;
+    int v;
+    if (c->oneshot_max_set)      // the caller's threshold replaces the table's one-shot rows
+        v = one_shot ? GA_VARIANT_ONESHOT_PUSH : (nbytes <= c->pipe_max_bytes ? GA_VARIANT_TWOSHOT_PIPE : GA_VARIANT_TWOSHOT_PUSH);
+    else
+        v = auto_from_table(c->world, nbytes);
+    // one-shot push stages `world` copies of the set in every rank's bucket
+    if (v == GA_VARIANT_ONESHOT_PUSH && nbytes * c->world > c->capacity_bytes) v = c->world <= 2 ? GA_VARIANT_TWOSHOT_PUSH : GA_VARIANT_TWOSHOT_PIPE;
+    if (v == GA_VARIANT_TWOSHOT_PIPE && (nbytes > c->pipe_max_bytes || c->world <= 2)) v = GA_VARIANT_TWOSHOT_PUSH;
+    return v;
 }
 
 int ga_auto_variant(int world, int n_local, size_t capacity_bytes, size_t nbytes) {
@@ -1524,7 +1556,7 @@ int ga_last_grid(const ga_ctx *c, int *blocks, int *threads) {
 int ga_set_option(ga_ctx *c, int option, int64_t value) {
     if (!c) return fail(GA_EINVAL, "NULL context");
     switch (option) {
-        case GA_OPT_ONESHOT_MAX_BYTES: c->oneshot_max_bytes = value < 0 ? 0 : (size_t)value; return GA_OK;
+        case GA_OPT_ONESHOT_MAX_BYTES: c->oneshot_max_bytes = value < 0 ? 0 : (size_t)value; c->oneshot_max_set = true; return GA_OK;
         case GA_OPT_TIMEOUT_MS: c->timeout_ns = value <= 0 ? 0 : (unsigned long long)value * 1000000ull; return GA_OK;
         case GA_OPT_MAX_BLOCKS: c->max_blocks_opt = value < 0 ? 0 : (int)value; return GA_OK;
         case GA_OPT_TRACE: {

@@ -220,6 +220,7 @@ struct ga_ctx {
     unsigned long long *trace_dev;  // GA_OPT_TRACE: kMaxBlocks * n_local * kTraceSlots words, or nullptr
     int pipe_group_opt;             // GA_OPT_PIPE_GROUP: tile slots per block per round (0 = automatic)
     size_t oneshot_max_bytes;
+    bool oneshot_max_set;           // GA_OPT_ONESHOT_MAX_BYTES was given: it replaces the table's one-shot rows
     size_t pipe_min_bytes;          // pipelined kernel: one round below min, 32 MiB rounds from min on; AUTO stops
     size_t pipe_max_bytes;          //   using it above max (N=4/8 sweeps: 3-10 % gain up to 128 MiB, a loss beyond)
     unsigned long long timeout_ns;

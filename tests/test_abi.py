@@ -95,23 +95,46 @@ def test_product_never_touches_the_oracle():
 
 
 def test_auto_variant_rules(built):
-    """AUTO as a pure host function: the thresholds fitted from the round-1 sweeps."""
+    """AUTO as a pure host function: the table read off the round-2 sweeps."""
     ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, HOSTED_DIRECT = 1, 2, 3, 4, 5, 6
     MiB = 1 << 20
     f = built.ga_auto_variant
-    # one rank per GPU, 8 ranks: one-shot push while (world-1)*S <= 8 MiB, pipelined up to 128 MiB, then plain push
+    # one rank per GPU, 8 ranks: one-shot push while (world-1)*S <= 8 MiB, one-round pipelined up to 32 MiB, then plain push
     assert f(8, 1, 64 * MiB, 4096) == ONESHOT_PUSH
     assert f(8, 1, 64 * MiB, MiB) == ONESHOT_PUSH
     assert f(8, 1, 64 * MiB, 1724320) == TWOSHOT_PIPE
-    assert f(8, 1, 64 * MiB, 64 * MiB) == TWOSHOT_PIPE
+    assert f(8, 1, 64 * MiB, 16 * MiB) == TWOSHOT_PIPE
+    assert f(8, 1, 64 * MiB, 64 * MiB) == TWOSHOT_PUSH
     assert f(8, 1, 1024 * MiB, 256 * MiB) == TWOSHOT_PUSH
+    assert f(4, 1, 64 * MiB, 1724320) == ONESHOT_PUSH and f(4, 1, 64 * MiB, 4 * MiB) == TWOSHOT_PIPE
     # one-shot push needs world * S of staging: without it, two-shot
     assert f(8, 1, 4 * MiB, MiB) == TWOSHOT_PIPE
-    # two ranks: one-shot up to 32 MiB
+    # two ranks: one-shot up to 32 MiB, never the pipelined kernel
     assert f(2, 1, 1024 * MiB, 16 * MiB) == ONESHOT_PUSH
-    assert f(2, 1, 1024 * MiB, 64 * MiB) == TWOSHOT_PIPE
+    assert f(2, 1, 1024 * MiB, 64 * MiB) == TWOSHOT_PUSH
+    assert f(2, 1, 16 * MiB, 16 * MiB) == TWOSHOT_PUSH
     # every rank hosted in one process: no exchange at all; a hosted sub-world uses the pull kernels
     assert f(4, 4, 64 * MiB, 64 * MiB) == HOSTED_DIRECT
     assert f(4, 2, 64 * MiB, 64 * MiB) == TWOSHOT and f(4, 2, 64 * MiB, 4096) == ONESHOT
     assert f(1, 1, 64 * MiB, MiB) == ONESHOT
     assert f(9, 1, MiB, 4) == -1 and f(2, 3, MiB, 4) == -1
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_auto_is_within_3_percent_of_the_best_variant_in_every_measured_row(built, world):
+    """north_star: "the variant is chosen per bucket size from measured bandwidth".  The committed
+    sweeps of this pool (profiles/r02_bench_nN_sweep.json: every fused variant timed at every size,
+    device-timed, max over ranks) are the measurement; for each row, what AUTO resolves to must have
+    been within 3 % (or 1.5 us, the harness's own jitter) of the quickest fused variant."""
+    import json
+    names = {3: "fused_oneshot_push", 4: "fused_twoshot_push", 5: "fused_twoshot_pipe", 1: "fused_oneshot", 2: "fused_twoshot"}
+    line = json.load(open(os.path.join(ROOT, "profiles", "r02_bench_n%d_sweep.json" % world)))
+    rows = [r for r in line["sweep"] if r.get("bytes")]
+    assert len(rows) >= 12
+    for r in rows:
+        fused = {k: v["us"] for k, v in r.items() if k.startswith("fused_") and k != "fused_auto"}
+        pick = built.ga_auto_variant(world, 1, (1 << 30) + 4096, r["bytes"])
+        t = fused[names[pick]]
+        best = min(fused.values())
+        assert t <= best * 1.03 or t - best <= 1.5, "world %d, %d bytes: AUTO -> %s %.1f us, best %.1f us (%s)" % (
+            world, r["bytes"], names[pick], t, best, min(fused, key=fused.get))
