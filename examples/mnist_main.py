@@ -156,8 +156,12 @@ def main(argv=None):
         distributed.init_process_group(backend=args.backend, init_method=args.init_method,
                                        rank=args.rank, world_size=args.world_size)
     device = torch.device("cuda", torch.cuda.current_device())
-    torch.manual_seed(0)                       # identical replicas: the reference never broadcasts weights
+    # The reference builds Net() on every rank with no seed and no broadcast (mnist/main.py:185), so its
+    # replicas start from DIFFERENT weights.  Here every rank builds its own and rank 0's are replicated
+    # over the peer mappings (ga_broadcast_tensors) -- no reliance on a shared seed.
     net = Net().to(device)
+    if args.world_size != 1:
+        ga.default_averager().broadcast_parameters(net, root=0)
     opt = torch.optim.Adam(net.parameters(), lr=args.learning_rate)
     if args.synthetic:
         train = SyntheticBatches(args.synthetic, args.batch_size, args.rank)
