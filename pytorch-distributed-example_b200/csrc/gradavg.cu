@@ -69,13 +69,15 @@ __device__ __forceinline__ void store_grad_vecs(const Seg &sg, uint32_t tile, in
 #pragma unroll
     for (int u = 0; u < NV; ++u) {
         const size_t e = base + (size_t)((u0 + u) * 32 + lane) * 4;
+        // __stcg = st.global.cg: the pointer comes out of the kernel parameters as a generic one; naming the
+        // state space keeps these STG instead of generic ST (and the gradients' next reader is another kernel: L2)
         if (aligned && e + 4 <= n) {
-            *(Vec *)(dst + e) = v[u];
+            __stcg((Vec *)(dst + e), v[u]);
         } else {
-            if (e + 0 < n) dst[e + 0] = v[u].x;
-            if (e + 1 < n) dst[e + 1] = v[u].y;
-            if (e + 2 < n) dst[e + 2] = v[u].z;
-            if (e + 3 < n) dst[e + 3] = v[u].w;
+            if (e + 0 < n) __stcg(dst + e + 0, v[u].x);
+            if (e + 1 < n) __stcg(dst + e + 1, v[u].y);
+            if (e + 2 < n) __stcg(dst + e + 2, v[u].z);
+            if (e + 3 < n) __stcg(dst + e + 3, v[u].w);
         }
     }
 }
@@ -88,13 +90,14 @@ struct Sink {
 };
 
 template <int NV>
-__device__ __forceinline__ void sink_store(const Sink &s, const Seg *sg, uint32_t tile, int lane, int u0, const Vec (&v)[NV]) {
-    if (sg) {
-        store_grad_vecs<NV>(*sg, tile, lane, u0, v);
+__device__ __forceinline__ void sink_store(const Sink &s, int si, uint32_t tile, int lane, int u0, const Vec (&v)[NV]) {
+    if (s.segs) {      // a tensor call: entry `si` of the pointer table is the tile's tensor (an index, not a Seg or a
+                       // pointer-or-null to one: those cost four registers or a local-memory copy -- ptxas -v)
+        store_grad_vecs<NV>(s.segs[si], tile, lane, u0, v);
     } else {
         Vec *d = s.recv + (size_t)tile * kTileVecs + u0 * 32 + lane;
 #pragma unroll
-        for (int u = 0; u < NV; ++u) d[u * 32] = v[u];
+        for (int u = 0; u < NV; ++u) __stcg(d + u * 32, v[u]);
     }
 }
 
@@ -106,10 +109,10 @@ template <int W> struct Batch { static constexpr int value = W <= 2 ? 4 : (W <= 
 // shard, may be nullptr) and to the sink.
 template <int W, int OP>
 __device__ __forceinline__ void reduce_tile(const Params &p, uint32_t tile, int lane, float wf,
-                                            Vec *own, const Sink &sink, const Seg *sg) {
+                                            Vec *own, const Sink &sink, int si) {
     constexpr int NB = Batch<W>::value;
     const size_t off = (size_t)tile * kTileVecs + lane;
-#pragma unroll
+#pragma unroll(W > 4 ? 1 : kLaneVecs)
     for (int u0 = 0; u0 < kLaneVecs; u0 += NB) {
         Vec v[W][NB];
 #pragma unroll
@@ -137,7 +140,7 @@ __device__ __forceinline__ void reduce_tile(const Params &p, uint32_t tile, int 
 #pragma unroll
             for (int u = 0; u < NB; ++u) __stcg(own + off + (u0 + u) * 32, acc[u]);
         }
-        sink_store<NB>(sink, sg, tile, lane, u0, acc);
+        sink_store<NB>(sink, si, tile, lane, u0, acc);
     }
 }
 
@@ -215,20 +218,16 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
     if (VARIANT == GA_VARIANT_ONESHOT) {
         // (3) every rank reduces every tile and writes its own copy of the result
         for (uint32_t t = first; t < T; t += stride) {
-            const Seg *sg = nullptr;
-            Seg sgv;
-            if (sink.segs) { sgv = sink.segs[find_seg(sink.segs, sink.n_seg, t)]; sg = &sgv; }
-            reduce_tile<W, OP>(p, t, lane, wf, nullptr, sink, sg);
+            const int si = sink.segs ? find_seg(sink.segs, sink.n_seg, t) : 0;
+            reduce_tile<W, OP>(p, t, lane, wf, nullptr, sink, si);
         }
     } else {
         // (3) reduce-scatter: rank r reduces shard r in place in its bucket (+ its own copy out)
         for (uint32_t i = first; i < p.shard_tiles; i += stride) {
             const uint32_t t = r * p.shard_tiles + i;
             if (t >= T) break;
-            const Seg *sg = nullptr;
-            Seg sgv;
-            if (sink.segs) { sgv = sink.segs[find_seg(sink.segs, sink.n_seg, t)]; sg = &sgv; }
-            reduce_tile<W, OP>(p, t, lane, wf, mysend, sink, sg);
+            const int si = sink.segs ? find_seg(sink.segs, sink.n_seg, t) : 0;
+            reduce_tile<W, OP>(p, t, lane, wf, mysend, sink, si);
         }
         // (4) barrier 2: shard column reduced everywhere
         const size_t mid_off = offsetof(Pad, mid) / 4 + (size_t)b * kMaxWorld + r;
@@ -242,14 +241,12 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
                 const int j = (r + jj) % W;
                 const uint32_t t = j * p.shard_tiles + i;
                 if (t >= T) continue;
-                const Seg *sg = nullptr;
-                Seg sgv;
-                if (sink.segs) { sgv = sink.segs[find_seg(sink.segs, sink.n_seg, t)]; sg = &sgv; }
+                const int si = sink.segs ? find_seg(sink.segs, sink.n_seg, t) : 0;
                 const Vec *src = (const Vec *)p.send[j] + (size_t)t * kTileVecs + lane;
                 Vec v[kLaneVecs];
 #pragma unroll
                 for (int u = 0; u < kLaneVecs; ++u) v[u] = __ldcg(src + u * 32);
-                sink_store<kLaneVecs>(sink, sg, t, lane, 0, v);
+                sink_store<kLaneVecs>(sink, si, t, lane, 0, v);
             }
         }
     }
@@ -288,7 +285,8 @@ __global__ void __launch_bounds__(kThreads, 2) ga_fused_kernel(const __grid_cons
 template <int W, int OP, typename SrcFn, typename OutFn>
 __device__ __forceinline__ void fold_tile(SrcFn src, float wf, int lane, OutFn out) {
     constexpr int NB = Batch<W>::value;
-#pragma unroll
+    // worlds above 4 keep W vectors per row in flight: unrolling the four rows on top of that spilled (ptxas -v)
+#pragma unroll(W > 4 ? 1 : kLaneVecs)
     for (int u0 = 0; u0 < kLaneVecs; u0 += NB) {
         Vec v[W][NB];
 #pragma unroll
@@ -387,12 +385,18 @@ __global__ void __launch_bounds__(kThreads, 2) ga_push_kernel(const __grid_const
             fold_tile<W, OP>([&](int s) { return mystage + ((size_t)s * Ts + i) * kTileVecs; }, wf, lane,
                              [&](int u0, const Vec(&acc)[NB]) {
                                  store_grad_vecs<NB>(sg, t, lane, u0, acc);
-#pragma unroll
-                                 for (int jj = 1; jj < W; ++jj) {
+                                 auto to_peer = [&](int jj) {
                                      const int j = (r + jj) % W;
                                      Vec *dst = (Vec *)p.gather[j] + (size_t)t * kTileVecs + u0 * 32 + lane;
 #pragma unroll
                                      for (int u = 0; u < NB; ++u) __stcg(dst + u * 32, acc[u]);
+                                 };
+                                 if constexpr (W > 4) {          // seven hoisted peer addresses spilled (ptxas -v)
+#pragma unroll 1
+                                     for (int jj = 1; jj < W; ++jj) to_peer(jj);
+                                 } else {
+#pragma unroll
+                                     for (int jj = 1; jj < W; ++jj) to_peer(jj);
                                  }
                              });
         }

@@ -83,8 +83,11 @@ def test_loss_curve_matches_oracle_averaging(built, world, variant):
 
 def test_overlapped_averaging_same_bits(built):
     """Bucketed averaging fired from grad hooks on a side stream during backward gives the same
-    gradients, bit for bit, as the single fused call after backward (hosted world of 3 replicas of
-    a 62-tensor ResNet-18-shaped parameter set with a chain of matmuls as backward)."""
+    gradients, bit for bit, as oracle/fold.c on the un-averaged gradients and as the single fused call
+    after backward (hosted world of 3 replicas of a 62-tensor ResNet-18-shaped parameter set with a chain
+    of matmuls as backward).  force=True: left to itself the object would decline to overlap a set this
+    small (tests/test_gpu_view.py covers that decision)."""
+    import oracle
     import pytorch_distributed_example_b200 as ga
     from pytorch_distributed_example_b200 import workloads
     torch.cuda.set_device(0)
@@ -111,7 +114,8 @@ def test_overlapped_averaging_same_bits(built):
 
     nets_a = make()
     avg = ga.GradAverager(local_world=world, device=0)
-    ov = ga.OverlappedAverager(nets_a, averager=avg, bucket_cap_bytes=8 << 20, max_blocks=8, variant="twoshot")
+    ov = ga.OverlappedAverager(nets_a, averager=avg, bucket_cap_bytes=8 << 20, max_blocks=8, variant="twoshot", force=True)
+    assert ov.enabled
     assert len(ov.buckets) >= 4
     for step in range(3):
         for r in range(world):
@@ -135,4 +139,11 @@ def test_overlapped_averaging_same_bits(built):
             assert pa.grad.cpu().numpy().tobytes() == pb.grad.cpu().numpy().tobytes()
     for pa, pb in zip(nets_a[0].parameters(), nets_a[2].parameters()):
         assert torch.equal(pa.grad, pb.grad)
+    # against the oracle itself: the same last step with no averaging at all, folded on the host
+    nets_c = make()
+    for r in range(world):
+        nets_c[r](xs[r] * 3).backward()
+    for i, pa in enumerate(nets_a[1].parameters()):
+        want = oracle.fold_average_c([list(nets_c[r].parameters())[i].grad.cpu().numpy().ravel() for r in range(world)])
+        assert pa.grad.cpu().numpy().tobytes() == want.tobytes(), "tensor %d differs from oracle/fold.c" % i
     avg.close()
