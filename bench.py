@@ -271,7 +271,8 @@ def modes_leg(avg, vavg, world, hosted, S, sets, dev, multi, timed_loop, nvlink_
                          "kernel": {"twoshot": "ga_fused_kernel<%d,2,f32avg>", "oneshot": "ga_fused_kernel<%d,1,f32avg>",
                                     "twoshot_pipe": "ga_push_pipe_kernel<%d,f32avg>"}[v] % world,
                          "kernel_ms": ms, "what": "the cross-GPU protocol kernel (pack -> exchange -> unpack, flags) run by the "
-                                                  "hosted world on this one GPU: the code path N > 1 ships",
+                                                  "hosted world on this one GPU: the code path N > 1 ships; a fraction above 1 means "
+                                                  "the 126 MB L2 served part of the algorithmic bytes (hosted ranks re-read each other's buckets)",
                          "algorithmic": "%d hosted ranks x %.2f x S bytes per launch" % (hosted, alg / hosted / S)})
     # view mode: every hosted rank's gradient lives in its view region
     views = [vavg.view_tensor(S, l) for l in range(hosted)]
@@ -284,10 +285,15 @@ def modes_leg(avg, vavg, world, hosted, S, sets, dev, multi, timed_loop, nvlink_
         out["view"]["bus_gbps_per_rank"] = S / (ms / 1e3) * bus_factor(world) / 1e9
         more.append(nvlink_roofline(ms, "ga_view_kernel<%d,f32avg>" % world, None))
     else:
-        alg = hosted * (2.0 + 2.0 * (world - 1) / world + 2.0) * S   # scatter read+write (W-1)/W each, fold read S + write S
+        alg = hosted * (2.0 * (world - 1) / world + 2.0) * S         # scatter: read + write (W-1)/W * S; fold: read S, write S
         out["view"]["hbm_gbps"] = alg / (ms / 1e3) / 1e9
+        vt = None
+        try:
+            vt = json.load(open(os.path.join(ROOT, "profiles", "traffic_view.json"))).get("dram_bytes_per_launch")
+        except Exception:
+            pass
         more.append({"bound": "hbm", "achieved": alg / (ms / 1e3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / hbm_peak,
-                     "traffic": None, "kernel": "ga_view_kernel<%d,f32avg>" % world, "kernel_ms": ms,
+                     "traffic": vt, "kernel": "ga_view_kernel<%d,f32avg>" % world, "kernel_ms": ms,
                      "algorithmic": "%d hosted ranks x (2(W-1)/W scatter + 2 fold) x S bytes" % hosted})
     if multi and vavg.has_multicast:
         ms, _ = timed_loop(lambda i: vavg.allreduce_view(S, variant="nvls"), k, w)
