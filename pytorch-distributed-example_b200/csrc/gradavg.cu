@@ -1449,11 +1449,14 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
     rc = drain_if_needed(c, stream);
     if (rc) return rc;
     const size_t bucket_bytes = (size_t)total * kTileBytes;
-    // Chunk = 1/32 of the set, between 1 MiB and host_chunk_bytes: the pipeline's fill and drain
-    // (first copy-in, last copy-out run alone) cost one chunk each.
-    size_t chunk = (bucket_bytes / 32 + kTileBytes - 1) / kTileBytes * kTileBytes;
+    // Chunk = 1/8 of the set, between 1 MiB and host_chunk_bytes (8 MiB): the pipeline's fill and drain
+    // (first copy-in, last copy-out run alone) cost one chunk each, and every chunk costs a handful of
+    // API calls.  Round-2 sweep at 64 MiB per rank (tools/e2e_chunk_sweep.py): 8 MiB chunks take 6.4 / 2.9 /
+    // 3.9 ms at N = 1 (4 hosted) / 2 / 4 where the former 2 MiB chunks took 7.6 / 3.6 / 4.5.
+    size_t chunk = (bucket_bytes / 8 + kTileBytes - 1) / kTileBytes * kTileBytes;
     if (chunk < ((size_t)1 << 20)) chunk = (size_t)1 << 20;
     if (chunk > c->host_chunk_bytes) chunk = c->host_chunk_bytes;
+    if (c->host_chunk_set) chunk = c->host_chunk_bytes;        // GA_OPT_HOST_CHUNK_BYTES given: exactly that
     if ((bucket_bytes + chunk - 1) / chunk > (size_t)kHostChunks)
         chunk = ((bucket_bytes + kHostChunks - 1) / kHostChunks + kTileBytes - 1) / kTileBytes * kTileBytes;
     const int n_chunks = (int)((bucket_bytes + chunk - 1) / chunk);
@@ -1475,6 +1478,8 @@ int ga_average_host(ga_ctx *c, void *const *host_ptrs, const int64_t *numel, int
     CUDA_TRY(cudaStreamWaitEvent(c->s_in, c->ev_start, 0));
     CUDA_TRY(cudaStreamWaitEvent(c->s_k, c->ev_start, 0));
     CUDA_TRY(cudaStreamWaitEvent(c->s_out, c->ev_start, 0));
+    // (A tapered schedule -- 1, 2, 4 MiB chunks at both ends to shorten the pipeline's fill and drain -- was
+    // measured and lost to uniform chunks, 6.9 against 6.5 ms: six more chunks of API calls and small copies.)
     for (int k = 0; k < n_chunks; ++k) {
         const size_t lo = (size_t)k * chunk, hi = lo + chunk < bucket_bytes ? lo + chunk : bucket_bytes;
         rc = copy_chunk(c, host_ptrs, numel, n_tensors, lo, hi, true, c->s_in);
@@ -1579,6 +1584,8 @@ int ga_set_option(ga_ctx *c, int option, int64_t value) {
         }
         case GA_OPT_HOST_CHUNK_BYTES:
             c->host_chunk_bytes = value < (int64_t)kTileBytes ? kTileBytes : ((size_t)value + kTileBytes - 1) / kTileBytes * kTileBytes;
+            c->host_chunk_set = value > 0;
+            if (value <= 0) c->host_chunk_bytes = (size_t)8 << 20;
             return GA_OK;
         case GA_OPT_PIPE_GROUP: c->pipe_group_opt = value < 0 ? 0 : (value > 64 ? 64 : (int)value); return GA_OK;
         case GA_OPT_VIEW_CHUNK_TILES: c->view_chunk_opt = value < 0 ? 0 : (value > 65536 ? 65536 : (int)value); return GA_OK;

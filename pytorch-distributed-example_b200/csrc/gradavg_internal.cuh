@@ -238,6 +238,7 @@ struct ga_ctx {
     cudaStream_t s_in, s_k, s_out;
     cudaEvent_t ev_start, ev_done, ev_in[kHostChunks], ev_k[kHostChunks];
     size_t host_chunk_bytes;
+    bool host_chunk_set;            // GA_OPT_HOST_CHUNK_BYTES was given: use exactly that chunk size
     // launches of one context must be ordered with respect to each other (the flag epoch and the
     // staging regions are per context): when the caller's stream changes, the new stream is made to
     // wait for the previous launch through this event (ga_order_stream)
