@@ -89,7 +89,7 @@ extern "C" {
 #define GA_OPT_TIMEOUT_MS        2   /* flag-wait timeout inside kernels; 0 = wait forever */
 #define GA_OPT_MAX_BLOCKS        3   /* cap on thread blocks per rank (0 = fill the device) */
 #define GA_OPT_TRACE             6   /* 1: the push kernels record per-block phase timestamps (globaltimer ns) */
-#define GA_OPT_HOST_CHUNK_BYTES  5   /* ga_average_host: largest chunk of the copy-in / reduce / copy-out pipeline */
+#define GA_OPT_HOST_CHUNK_BYTES  5   /* ga_average_host: chunk size of the copy-in / reduce / copy-out pipeline (0 = default: 1/8 of the set, 1-8 MiB) */
 #define GA_OPT_PIPE_GROUP        4   /* TWOSHOT_PIPE: tile slots per block per round (0 = automatic) */
 #define GA_OPT_VIEW_CHUNK_TILES  7   /* GA_VARIANT_VIEW: 2 KiB tiles per chunk (0 = automatic) */
 #define GA_OPT_VIEW_ONESHOT_MAX_BYTES 8 /* GA_VARIANT_VIEW: sets up to this size take the one-shot form (every rank receives
