@@ -231,27 +231,36 @@ __global__ void __launch_bounds__(kThreads, 2) ga_view_kernel(const __grid_const
                 __threadfence_block();
                 ring_wait(q);
                 const uint32_t i0 = (k + q * nb) * C;
-                for (uint32_t it = dw; it < C * kLaneVecs; it += ndata) {
-                    const uint32_t i = i0 + it / kLaneVecs;
+                // items = (tile, group of NB 512-byte rows): W * NB vectors in flight per thread.  Small worlds
+                // take more rows per item, or the fold is latency-bound on its local loads (2 x 16 B per thread
+                // at world 2 could not feed the link)
+                constexpr int NB = W <= 2 ? 4 : (W <= 4 ? 2 : 1);
+                constexpr uint32_t kGroups = kLaneVecs / NB;
+                for (uint32_t it = dw; it < C * kGroups; it += ndata) {
+                    const uint32_t i = i0 + it / kGroups;
                     const uint32_t t = one ? i : r * Ts + i;                   // one-shot: chunks run over all T tiles
                     if ((!one && i >= Ts) || t >= T) continue;
-                    const size_t row = (size_t)(it % kLaneVecs) * 32 + lane;
-                    Vec v[W];
+                    const size_t row = (size_t)(it % kGroups) * NB * 32 + lane;
+                    Vec v[NB][W];
 #pragma unroll
                     for (int s = 0; s < W; ++s) {
                         const Vec *src = s == r ? (const Vec *)p.view[r] + (size_t)t * kTileVecs
                                          : one  ? mystage + ((size_t)(s < r ? s : s - 1) * T + t) * kTileVecs
                                                 : mystage + ((size_t)s * Ts + i) * kTileVecs;
-                        v[s] = __ldcg(src + row);
-                    }
-                    const Vec acc = fold_vecs<OP, W>(v, wf);
-                    if (one) {
-                        __stcg((Vec *)p.view[r] + (size_t)t * kTileVecs + row, acc);
-                    } else {
 #pragma unroll
-                        for (int jj = 0; jj < W; ++jj) {
-                            const int j = (r + jj) % W;
-                            __stcg((Vec *)p.view[j] + (size_t)t * kTileVecs + row, acc);
+                        for (int u = 0; u < NB; ++u) v[u][s] = __ldcg(src + row + u * 32);
+                    }
+#pragma unroll
+                    for (int u = 0; u < NB; ++u) {
+                        const Vec acc = fold_vecs<OP, W>(v[u], wf);
+                        if (one) {
+                            __stcg((Vec *)p.view[r] + (size_t)t * kTileVecs + row + u * 32, acc);
+                        } else {
+#pragma unroll
+                            for (int jj = 0; jj < W; ++jj) {
+                                const int j = (r + jj) % W;
+                                __stcg((Vec *)p.view[j] + (size_t)t * kTileVecs + row + u * 32, acc);
+                            }
                         }
                     }
                 }
