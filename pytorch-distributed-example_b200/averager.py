@@ -142,8 +142,20 @@ class GradAverager:
             self.close()
         self._create(max(need_bytes, 32 << 20))     # room for two one-shot staging halves of small sets
 
+    def _release_views(self):
+        """Adopted gradients point into the view region: before it is freed, every gradient that still lives
+        there moves to memory of its own (same values), so no tensor is left pointing at freed memory."""
+        ad, self._adopted = self._adopted, None
+        if ad is None:
+            return
+        for p, a in zip(ad[3], ad[1]):
+            g = p.grad
+            if g is not None and g.data_ptr() == a:
+                p.grad = g.clone()
+
     def close(self):
         if self._ctx is not None:
+            self._release_views()
             if torch.cuda.is_available():
                 torch.cuda.synchronize()
             if not self._local and self.world_size > 1:
@@ -161,6 +173,7 @@ class GradAverager:
     def __del__(self):
         try:
             if self._ctx is not None:
+                self._release_views()
                 self._lib.ga_destroy(self._ctx)
                 self._ctx = None
         except Exception:

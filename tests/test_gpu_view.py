@@ -155,7 +155,13 @@ def test_adopted_gradients_train_like_the_drop_in_mode(built, world):
             avg.average_gradients_local(nets)
             want = _fold([host[r][0].ravel() for r in range(world)])
             assert list(nets[1].parameters())[0].grad.cpu().numpy().tobytes() == want.tobytes()
+        before = [p.grad.clone() for p in nets[0].parameters()]
         avg.close()
+        if mode == "view":
+            # close() frees the view region: the gradients must have moved out of it, values intact
+            torch.zeros(32 << 20, device="cuda")                      # reuse whatever was freed
+            for b, p in zip(before, nets[0].parameters()):
+                assert torch.equal(b, p.grad)
     assert curves["view"] == curves["dropin"]
 
 
