@@ -61,7 +61,7 @@ extern "C" {
 #define GA_ETIMEOUT     -5   /* a kernel gave up waiting for a peer's flag (see ga_status) */
 
 /* variant of the reduction */
-#define GA_VARIANT_AUTO     0   /* chosen from the byte count, see ga_set_option(GA_OPT_ONESHOT_MAX_BYTES) */
+#define GA_VARIANT_AUTO     0   /* chosen from world size and byte count by a table read off measured sweeps (ga_auto_variant) */
 #define GA_VARIANT_ONESHOT  1   /* every rank reads all `world` buckets: 1 barrier, (world-1)*S ingress */
 #define GA_VARIANT_TWOSHOT  2   /* reduce-scatter + all-gather by peer reads: 2 barriers, 2(world-1)/world*S */
 #define GA_VARIANT_ONESHOT_PUSH 3 /* every rank STORES its set into every peer's staging slot, local fold   */
@@ -256,7 +256,8 @@ int ga_rank(const ga_ctx *ctx);
 int ga_n_local(const ga_ctx *ctx);
 size_t ga_capacity(const ga_ctx *ctx);
 
-/* What AUTO resolves to for `nbytes` (GA_VARIANT_ONESHOT or GA_VARIANT_TWOSHOT). */
+/* What AUTO resolves to for a tensor-list call of `nbytes` on this context (one of GA_VARIANT_ONESHOT ...
+ * GA_VARIANT_HOSTED_DIRECT; never VIEW or NVLS, which belong to ga_average_view). */
 int ga_pick_variant(const ga_ctx *ctx, size_t nbytes);
 
 /* The same rule without a context (pure host arithmetic, no GPU needed): what AUTO would pick for a
