@@ -235,6 +235,26 @@ def nvlink_counters(index):
         return None
 
 
+def view_averager(nbytes, local_world):
+    """A context with a view region of `nbytes`: with an NVSwitch multicast mapping where the box allows it
+    (GPU support and descriptor passing between the rank processes), else shared through CUDA-IPC alone.
+    Every rank sees the same failure, so the retry stays collective."""
+    import pytorch_distributed_example_b200 as ga
+    for multicast in (True, False):
+        a = ga.GradAverager(local_world=local_world, device=0, capacity_bytes=nbytes) if local_world else ga.GradAverager(capacity_bytes=nbytes)
+        try:
+            a.create_view(nbytes, multicast=multicast)
+            return a
+        except ga.GradAvgError as e:
+            stage("view region with multicast=%s failed (%s)%s" % (multicast, e, ": retrying without" if multicast else ""))
+            try:
+                a.close()
+            except Exception:
+                pass
+            if not multicast:
+                raise
+
+
 def modes_leg(avg, vavg, world, hosted, S, sets, dev, multi, timed_loop, nvlink_roofline, hbm_peak):
     """The same averaging through the library's other modes, 64 MiB per rank, each with its own roofline:
       dropin_*   Trainer.average_gradients on ordinary gradient tensors (pack + exchange + unpack), other variants
@@ -571,8 +591,7 @@ def main():
         # ---- the other ways to make the same call (same gradients, same result bits unless said otherwise) ----
         stage("modes leg")
         # the view region pins its context's size, so the in-place modes get a context of their own
-        vavg = ga.GradAverager(capacity_bytes=S) if multi else ga.GradAverager(local_world=world, device=0, capacity_bytes=S)
-        vavg.create_view(S, multicast=True)
+        vavg = view_averager(S, world if not multi else 0)
         line["modes"], more = modes_leg(avg, vavg, world, hosted, S, sets, dev, multi, timed_loop, nvlink_roofline, hbm_peak)
         line["roofline_more"] = more
         if multi:
@@ -696,8 +715,7 @@ def sweep_multi(avg, world, dev, dist, max_bytes, rank=0):
              256 << 20, 1 << 30]
     sizes = [s for s in sizes if s <= max_bytes]
     avg.reserve(max(sizes) + 4096)
-    vavg = ga.GradAverager(capacity_bytes=max(sizes) + 4096)
-    vavg.create_view(max(sizes) + 4096, multicast=True)
+    vavg = view_averager(max(sizes) + 4096, 0)
     out = []
 
     def timed(fn, iters, warm=5):

@@ -218,6 +218,9 @@ int ga_view_export(ga_ctx *ctx, unsigned char out[GA_VIEW_HANDLE_BYTES]);
 int ga_view_open(ga_ctx *ctx, const unsigned char *handles);
 int ga_view_bind(ga_ctx *ctx);
 void *ga_view_ptr(ga_ctx *ctx, int local_rank);
+/* Unmaps and frees the view region again (collective: barrier first, no peer may still be using it), e.g. to
+ * create it anew without GA_VIEW_MULTICAST after ga_view_open failed to fetch the peers' descriptors. */
+int ga_view_destroy(ga_ctx *ctx);
 size_t ga_view_bytes(const ga_ctx *ctx);
 int ga_view_has_multicast(const ga_ctx *ctx);
 

@@ -44,6 +44,7 @@ SIGNATURES = {
     "ga_view_open": (_c.c_int, [_c.c_void_p, _c.c_char_p]),
     "ga_view_bind": (_c.c_int, [_c.c_void_p]),
     "ga_view_ptr": (_c.c_void_p, [_c.c_void_p, _c.c_int]),
+    "ga_view_destroy": (_c.c_int, [_c.c_void_p]),
     "ga_view_bytes": (_c.c_size_t, [_c.c_void_p]),
     "ga_view_has_multicast": (_c.c_int, [_c.c_void_p]),
     "ga_multicast_supported": (_c.c_int, [_c.c_int]),

@@ -350,7 +350,17 @@ class GradAverager:
     # -- gradients as views of the peer-mapped region ---------------------------
     def _create_view(self, nbytes, multicast):
         """Collective: allocates the view region and maps every peer's (mnist/main.py:199-203's group
-        carries the handles, like the bucket's)."""
+        carries the handles, like the bucket's).  If the multicast kind cannot be set up on this box (the
+        descriptors cannot be passed between the rank processes, the driver refuses the multicast object)
+        every rank sees the same error, and the region is made again without it."""
+        if multicast:
+            try:
+                return self._create_view_kind(nbytes, True)
+            except GradAvgError:
+                check(self._lib.ga_view_destroy(self._ctx))
+        return self._create_view_kind(nbytes, False)
+
+    def _create_view_kind(self, nbytes, multicast):
         flags = _lib.VIEW_MULTICAST if multicast else 0
         check(self._lib.ga_view_create(self._ctx, int(nbytes), flags))
         if self._local or self.world_size == 1:

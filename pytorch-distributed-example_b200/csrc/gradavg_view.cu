@@ -496,6 +496,7 @@ static_assert(sizeof(ViewHandle) == GA_VIEW_HANDLE_BYTES, "view handle size");
 
 // Duplicates descriptor `fd` of process `pid` into this process (Linux >= 5.6; same user).
 int fetch_fd(int pid, int fd) {
+    if (getenv("GA_TEST_FAIL_FETCH_FD")) { errno = EPERM; return -1; }     // test hook: a box where pidfd_getfd is not permitted
     if (pid == (int)getpid()) return dup(fd);
     const int pidfd = (int)syscall(SYS_pidfd_open, pid, 0);
     if (pidfd < 0) return -1;
@@ -773,6 +774,15 @@ int ga_view_bind(ga_ctx *c) {
     CU_TRY(g_drv.MulticastBindMem(c->view_mc_handle, 0, c->view_mem[c->rank_base], 0, c->view_map_bytes, 0));
     c->view_mc_bound = true;
     return map_handle(c, c->view_mc_handle, c->view_map_bytes, kViewGranularity, &c->view_mc);
+}
+
+int ga_view_destroy(ga_ctx *c) {
+    if (!c) return fail(GA_EINVAL, "NULL context");
+    if (c->view_kind == 0) return GA_OK;
+    ENTER_DEVICE(c->device);
+    CUDA_TRY(cudaDeviceSynchronize());
+    ga_view_release(c, true);
+    return GA_OK;
 }
 
 void *ga_view_ptr(ga_ctx *c, int local_rank) {

@@ -447,3 +447,46 @@ def loss_curve_world(rank, world, port, q):
         import traceback
         out["fail"].append("exception: %s\n%s" % (e, traceback.format_exc()))
     q.put(out)
+
+
+def fallback_world(rank, world, port, q):
+    """A box on which the rank processes may not fetch each other's descriptors (pidfd_getfd refused): the
+    multicast kind of view region cannot be set up, every rank sees the same error, and the region is made
+    again through CUDA-IPC alone.  In-place averaging must work and be bit-exact; NVLS must be refused."""
+    import numpy as np
+    import torch
+    import torch.distributed as tdist
+    import oracle
+    import pytorch_distributed_example_b200 as ga
+    from pytorch_distributed_example_b200 import distributed as dist
+
+    out = {"rank": rank, "fail": [], "launches": 0}
+    try:
+        os.environ["GA_TEST_FAIL_FETCH_FD"] = "1"
+        os.environ.setdefault("GA_TIMEOUT_MS", "8000")
+        dist.init_process_group(backend="nccl", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+        avg = ga.GradAverager(capacity_bytes=8 << 20)
+        avg.create_view(8 << 20, multicast=True)
+        if avg.has_multicast:
+            out["fail"].append("multicast mapping although the descriptors could not be fetched")
+        n = 1_000_003
+        host = [np.random.default_rng(40 + r).standard_normal(n).astype(np.float32) for r in range(world)]
+        v = avg.view_tensor(n * 4)
+        v.copy_(torch.from_numpy(host[rank]))
+        avg.allreduce_view(n * 4, variant="view")
+        avg.check_status()
+        if v.cpu().numpy().tobytes() != oracle.fold_average_c(host).tobytes():
+            out["fail"].append("view kernel on the CUDA-IPC region differs from the oracle")
+        try:
+            avg.allreduce_view(n * 4, variant="nvls")
+            out["fail"].append("nvls accepted without a multicast mapping")
+        except ga.GradAvgError:
+            pass
+        out["launches"] = avg.launch_count
+        tdist.barrier()
+        avg.close()
+        tdist.destroy_process_group()
+    except Exception as e:
+        import traceback
+        out["fail"].append("exception: %s\n%s" % (e, traceback.format_exc()))
+    q.put(out)

@@ -52,6 +52,12 @@ def test_eight_ranks_ipc():
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_view_region_falls_back_to_cuda_ipc_two_ranks():
+    """Descriptor passing refused (test hook): the view region is re-made without multicast, still bit-exact."""
+    _run(2, "nccl", worker="fallback_world", timeout=200, min_launches=0)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_large_sets_two_ranks():
     """256 MiB and ~1 GiB per rank (configs[3]'s upper end) through two-shot push, AUTO and the view kernel."""
     _run(2, "nccl", worker="big_world", timeout=400, min_launches=7)
