@@ -188,3 +188,42 @@ def test_init_process_group_selects_the_ranks_gpu(monkeypatch):
     monkeypatch.setenv("LOCAL_RANK", "3")
     distributed.init_process_group(backend="gloo", rank=11, world_size=16)
     assert chosen[-1] == 3
+
+
+def test_overlap_decision_is_a_pure_function_of_sizes():
+    """configs[4]: hook-driven overlap is only worth its host cost when the exchange it could hide is longer;
+    the model (fitted to the round-2 bench) declines ResNet-18-sized sets on NVLink and accepts GB-sized ones."""
+    from pytorch_distributed_example_b200 import workloads
+    from pytorch_distributed_example_b200.overlap import overlap_pays, plan_buckets
+    numels = [workloads.numel(s) for s in workloads.resnet18_shapes()]
+    buckets = plan_buckets(numels, 16 << 20)
+    assert sorted(i for b in buckets for i in b) == list(range(62)) and buckets[0][0] == 61     # reverse order, every tensor once
+    for world in (2, 4, 8):
+        pays, exchange_us, overhead_us = overlap_pays(numels, world, len(buckets))
+        assert not pays and 50 < exchange_us < 200 and overhead_us > 2 * exchange_us
+    pays, exchange_us, overhead_us = overlap_pays([50_000_000] * 30, 8, 30)                     # 6 GB of gradients
+    assert pays and exchange_us > 5 * overhead_us
+    assert overlap_pays(numels, 1, 4)[0] is False                                               # one rank: nothing to exchange
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")
+def test_new_entry_points_fail_loudly_without_gpu():
+    """The round-2 entry points (views, broadcast, the no-allocation variant and its status call) have no
+    CPU fallback either: without a device they return an error code and a message, and compute nothing."""
+    import ctypes
+    import pytorch_distributed_example_b200 as ga
+    lib = ga.load_library()
+    assert lib.ga_multicast_supported(0) == 0
+    assert lib.ga_view_create(None, 1 << 20, 0) == -1 and lib.ga_average_view(None, 1024, 0, None, 0) == -1
+    assert lib.ga_view_bytes(None) == 0 and lib.ga_view_has_multicast(None) == 0 and lib.ga_view_destroy(None) == -1
+    assert lib.ga_broadcast_tensors(None, None, None, 0, 0, None) == -1
+    numel = (ctypes.c_int64 * 1)(16)
+    ptrs = (ctypes.c_void_p * 2)(4096, 8192)
+    assert lib.ga_average_static(2, 0, ptrs, numel, 1, None, 0) == -2 and b"cuda" in lib.ga_last_error().lower()
+    assert lib.ga_static_status(0, None) == -2
+    assert lib.ga_average_static(2, 0, ptrs, (ctypes.c_int64 * 1)(3_000_000), 1, None, 0) == -3     # size check comes before any CUDA call
+    avg = ga.GradAverager(local_world=2)
+    with pytest.raises(ga.GradAvgError):
+        avg.adopt([torch.nn.Linear(3, 3), torch.nn.Linear(3, 3)])
+    with pytest.raises(ga.GradAvgError):
+        avg.broadcast_([[torch.zeros(4)], [torch.zeros(4)]])

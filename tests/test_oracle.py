@@ -105,3 +105,28 @@ def test_shape_tables():
     assert sum(oracle.numel_of(oracle.MNIST_CNN_SHAPES)) == 431080
     rs = oracle.resnet18_shapes()
     assert len(rs) == 62 and sum(oracle.numel_of(rs)) == 11689512
+
+
+def test_wide_fold_is_the_correctly_rounded_sum_and_differs_from_the_rank_order():
+    """Oracle of the opt-in NVSwitch variant (fold.c: oracle_fold_wide_average_f32): binary64 sum rounded once,
+    then the binary32 division.  C and numpy agree bit for bit; against exact rational arithmetic it is the
+    correctly rounded sum; and it is NOT the rank-order fold (last-bit differences on a large share of elements),
+    which is why that variant is opt-in and judged against this function instead."""
+    from fractions import Fraction
+    import numpy as np
+    import oracle
+    rng = np.random.default_rng(3)
+    for world in (2, 3, 4, 8):
+        host = [rng.standard_normal(20_000).astype(np.float32) for _ in range(world)]
+        wide_c, wide_np = oracle.fold_wide_average_c(host), oracle.fold_wide_average(host)
+        assert wide_c.tobytes() == wide_np.tobytes()
+        sums = oracle.fold_wide_average_c(host, divide=False)
+        for i in range(0, 20_000, 997):
+            exact = sum(Fraction(float(h[i])) for h in host)
+            got = Fraction(float(sums[i]))
+            ulp = Fraction(float(np.spacing(np.float32(abs(float(sums[i]))))))
+            assert abs(got - exact) <= ulp / 2
+        rank_order = oracle.fold_average_c(host)
+        differ = float((wide_c != rank_order).mean())
+        assert (differ == 0.0) if world == 2 else (0.02 < differ < 0.8)
+        assert oracle.backward_error(rank_order, wide_c, host) <= 1e-6
