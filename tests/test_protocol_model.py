@@ -1,4 +1,4 @@
-"""CPU: an executable model of the cross-rank flag protocol of csrc/gradavg.cu.
+"""CPU: an executable model of the cross-rank flag protocol of csrc/gradavg.cu and csrc/gradavg_view.cu.
 
 Every (rank, block) of every launch is a coroutine that performs the same steps, in the same order,
 as the CUDA kernels (waits on `done` / `ready` / `mid` words, bucket / staging / gather accesses,
@@ -16,12 +16,14 @@ import random
 import pytest
 
 ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE = 1, 2, 3, 4, 5
+VIEW = 7            # ga_view_kernel (csrc/gradavg_view.cu): gradients live in the peer-mapped region, averaged in place
+FLAG_ROWS = 16      # the view kernel indexes the flag rows by chunk, not by block
 
 
 class Rank:
     def __init__(self, world, blocks):
-        self.ready = [[0] * world for _ in range(blocks)]
-        self.mid = [[0] * world for _ in range(blocks)]
+        self.ready = [[0] * world for _ in range(max(blocks, FLAG_ROWS))]
+        self.mid = [[0] * world for _ in range(max(blocks, FLAG_ROWS))]
         self.done = [0] * world
         self.epoch = 0
         self.last_kind = 0
@@ -195,6 +197,113 @@ class World:
                 self.ranks[j].done[r] = last_epoch
         yield "ok"
 
+
+    # ---- ga_view_kernel: one coroutine per ROLE-WARP GROUP of a block -------------------------------
+    # A scatter block is its data warps (stores, then a tick in shared memory) and its publisher (waits
+    # for the tick, raises ready[c][r] everywhere); a fold block is its poller (waits for ready[c] from
+    # every rank), its data warps (fold, store the result into EVERY rank's region) and its publisher
+    # (mid[c][r]); the poller ends the block by waiting for mid[c] from every rank.  The data warps may
+    # run ahead of the publisher, as in the kernel.  `grads` is the view region itself (in place).
+    def view_parts(self, r, k, call, T, launch):
+        W, me = self.W, self.ranks[r]
+        epoch, C, nb, one = launch["epoch"], launch["chunk"], launch["nb"], launch["oneshot"]
+        Ts = T if one else -(-T // W)
+        NC = -(-Ts // C)
+        chunks = list(range(k, NC, nb))
+        fold = ("out", call)
+        sh = {"issued_s": 0, "issued_f": 0, "ready": 0}          # the block's shared-memory words
+
+        def expect(cell, want, what):
+            assert cell == want, "%s: call %d rank %d block-pair %d read %r, expected %r" % (what, call, r, k, cell, want)
+
+        def epilogue():
+            me.finished += 1
+            if me.finished == launch["blocks"]:
+                me.finished = 0
+                me.epoch = epoch
+                me.last_kind = 0
+                for j in range(W):
+                    self.ranks[j].done[r] = epoch
+            yield "ok"
+
+        def slot(s, j):                      # one-shot: the slot rank j keeps for source s
+            return s if s < j else s - 1
+
+        def scatter_data():
+            for s_ in range(W):
+                while me.done[s_] - (epoch - 1) < 0:
+                    yield "blocked"
+            for q, c in enumerate(chunks):
+                for i in range(c * C, min((c + 1) * C, Ts)):
+                    for jj in range(1, W):
+                        j = (r + jj) % W
+                        t = i if one else j * Ts + i
+                        if t >= T:
+                            continue
+                        expect(me.grads[t], ("in", call, r, t), "view scatter source")
+                        self.ranks[j].store("stage", ((slot(r, j), t) if one else (r, i)), ("in", call, r, t))
+                        yield "ok"
+                sh["issued_s"] = q + 1
+                yield "ok"
+            yield from epilogue()
+
+        def scatter_publisher():
+            for q, c in enumerate(chunks):
+                while sh["issued_s"] < q + 1:
+                    yield "blocked"
+                for j in range(W):
+                    self.ranks[j].ready[c][r] = epoch
+                yield "ok"
+            yield from epilogue()
+
+        def fold_poller():
+            for q, c in enumerate(chunks):
+                for s_ in range(W):
+                    while me.ready[c][s_] - epoch < 0:
+                        yield "blocked"
+                sh["ready"] = q + 1
+                yield "ok"
+            if not one:
+                for c in chunks:
+                    for s_ in range(W):
+                        while me.mid[c][s_] - epoch < 0:
+                            yield "blocked"
+            yield from epilogue()
+
+        def fold_data():
+            for q, c in enumerate(chunks):
+                while sh["ready"] < q + 1:
+                    yield "blocked"
+                for i in range(c * C, min((c + 1) * C, Ts)):
+                    t = i if one else r * Ts + i
+                    if t >= T:
+                        continue
+                    for s_ in range(W):
+                        if s_ == r:
+                            expect(me.grads[t], ("in", call, r, t), "view fold, own tile")
+                        else:
+                            key = ("stage", slot(s_, r), t) if one else ("stage", s_, i)
+                            expect(me.send.get(key), ("in", call, s_, t), "view fold, staged tile")
+                        yield "ok"
+                    for jj in range(W if not one else 1):
+                        self.ranks[(r + jj) % W].grads[t] = fold + (t,)
+                        yield "ok"
+                sh["issued_f"] = q + 1
+                yield "ok"
+            yield from epilogue()
+
+        def fold_publisher():
+            for q, c in enumerate(chunks):
+                while sh["issued_f"] < q + 1:
+                    yield "blocked"
+                if not one:
+                    for j in range(W):
+                        self.ranks[j].mid[c][r] = epoch
+                yield "ok"
+            yield from epilogue()
+
+        return [scatter_data(), scatter_publisher(), fold_poller(), fold_data(), fold_publisher()]
+
     # ---- scheduler ----------------------------------------------------------------------------------
     def run(self, calls):
         """calls: list of (variant, tiles).  Each rank launches them in order; launch k+1 of a rank
@@ -223,7 +332,15 @@ class World:
                         blocks, rounds = B, 1
                     launch = {"epoch": me.epoch + 1, "rounds": rounds, "group": group, "blocks": blocks,
                               "dbuf": variant == ONESHOT_PUSH and T <= 6}      # "fits two halves" for small sets
-                    active[r] = [self.block(r, b, call, variant, T, launch) for b in range(blocks)]
+                    if variant == VIEW:
+                        one = T <= 2 and W > 1                                 # small sets take the one-shot form
+                        chunk = 1 if T <= 6 else 2
+                        NC = -(-(T if one else Ts) // chunk)
+                        nb = min(B, NC)
+                        launch.update(chunk=chunk, nb=nb, oneshot=one, blocks=5 * nb)
+                        active[r] = [g for k in range(nb) for g in self.view_parts(r, k, call, T, launch)]
+                    else:
+                        active[r] = [self.block(r, b, call, variant, T, launch) for b in range(blocks)]
                     active[r] = [(g, call, T) for g in active[r]]
                     next_call[r] += 1
             runnable = [(r, k) for r in range(W) for k in range(len(active[r]))]
@@ -265,7 +382,7 @@ class World:
 @pytest.mark.parametrize("world", [2, 3, 4])
 @pytest.mark.parametrize("blocks", [1, 3])
 def test_random_interleavings_mixed_variants(world, blocks):
-    variants = [ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE]
+    variants = [ONESHOT, TWOSHOT, ONESHOT_PUSH, TWOSHOT_PUSH, TWOSHOT_PIPE, VIEW, VIEW]
     for seed in range(60):
         rng = random.Random(1000 * world + 10 * blocks + seed)
         calls = [(rng.choice(variants), rng.choice([1, 2, 5, 6, 7, 13])) for _ in range(8)]
@@ -308,6 +425,35 @@ def test_model_catches_single_buffer_without_wait():
     for seed in range(40):
         try:
             Broken(3, 1, seed).run([(ONESHOT_PUSH, 4)] * 6)
+        except AssertionError:
+            caught += 1
+    assert caught > 0
+
+
+def test_view_kernel_alone_and_back_to_back():
+    """ga_view_kernel's chunk flags, role split and one-shot form, launch after launch with skew."""
+    for world in (2, 3, 4):
+        for blocks in (1, 2, 3):
+            for seed in range(25):
+                rng = random.Random(7 * world + blocks + 100 * seed)
+                World(world, blocks, seed).run([(VIEW, rng.choice([1, 2, 3, 5, 7, 13, 16])) for _ in range(6)])
+
+
+def test_model_catches_a_fold_that_does_not_wait_for_its_own_scatter():
+    """One-shot form: the fold overwrites a tile in place, so it must not run before this rank's own scatter
+    block has sent that tile -- the poller waits for all W ready words, its own included.  Drop that and the
+    model must see a scatter reading an already averaged tile."""
+    class Broken(World):
+        def view_parts(self, r, k, call, T, launch):
+            parts = super().view_parts(r, k, call, T, launch)
+            me = self.ranks[r]
+            for c in range(FLAG_ROWS):
+                me.ready[c][r] = 1 << 30              # my own ready words look raised from the start
+            return parts
+    caught = 0
+    for seed in range(60):
+        try:
+            Broken(2, 1, seed).run([(VIEW, 2)] * 4)
         except AssertionError:
             caught += 1
     assert caught > 0
